@@ -1,0 +1,97 @@
+"""ctypes binding of the C ABI in include/mm_masking_b200.h.
+
+The shared library is built in-tree by `__graft_entry__.build()` (plain nvcc, sm_100a) and
+holds every CUDA kernel of this package.  There is no fallback: if the library is missing or
+CUDA is unavailable the ops raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmm_masking_b200.so")
+
+F32, F64 = 0, 1
+PT2PL, PT2PT = 0, 1
+LOSS_NONE, LOSS_HUBER, LOSS_CAUCHY = 0, 1, 2
+
+
+class IcpParams(C.Structure):
+    """mirror of `mmb_icp_params`"""
+    _fields_ = [
+        ("N", C.c_int32), ("n", C.c_int32), ("m", C.c_int32), ("target_cols", C.c_int32),
+        ("dtype", C.c_int32), ("icp_type", C.c_int32), ("dim", C.c_int32), ("max_iterations", C.c_int32),
+        ("differentiable", C.c_int32), ("const_iter", C.c_int32), ("use_trim", C.c_int32),
+        ("loss_kind", C.c_int32), ("has_weight", C.c_int32), ("save_for_backward", C.c_int32),
+        ("nn_slices", C.c_int32), ("reserved", C.c_int32),
+        ("tolerance", C.c_double), ("trim_dist", C.c_double), ("loss_metric", C.c_double),
+        ("tanh_steepness", C.c_double), ("match_ratio_thresh", C.c_double),
+    ]
+
+
+# name -> (restype, argtypes); tests check that every one of these is exported.
+_P = C.c_void_p
+SIGNATURES = {
+    "mmb_abi_version": (C.c_int, []),
+    "mmb_status_string": (C.c_char_p, [C.c_int]),
+    "mmb_last_cuda_error": (C.c_char_p, []),
+    "mmb_icp_workspace_bytes": (C.c_size_t, [C.POINTER(IcpParams)]),
+    "mmb_icp_saved_bytes": (C.c_size_t, [C.POINTER(IcpParams)]),
+    "mmb_icp_forward": (C.c_int, [C.POINTER(IcpParams)] + [_P] * 14 + [C.c_size_t, _P]),
+    "mmb_icp_backward": (C.c_int, [C.POINTER(IcpParams)] + [_P] * 11 + [C.c_size_t, _P]),
+    "mmb_nn_workspace_bytes": (C.c_size_t, [C.c_int32] * 4),
+    "mmb_nn_search": (C.c_int, [C.c_int32] * 7 + [_P] * 4 + [C.c_size_t, _P]),
+    "mmb_fp32_probe": (C.c_int, [C.c_int32] * 3 + [_P, _P]),
+}
+
+_lib = None
+
+
+class MmbError(RuntimeError):
+    pass
+
+
+def load_library(path: str | None = None):
+    """dlopen the kernel library and bind every symbol of the header."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    path = path or LIB_PATH
+    if not os.path.exists(path):
+        raise MmbError(
+            f"{path} not found: build the CUDA library first (python -c 'import __graft_entry__ as g; g.build()'). "
+            "mm_masking_b200 has no CPU fallback.")
+    lib = C.CDLL(path)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = res, args
+    if lib.mmb_abi_version() != 1:
+        raise MmbError("libmm_masking_b200.so ABI version mismatch")
+    _lib = lib
+    return lib
+
+
+def check(status: int, what: str):
+    if status == 0:
+        return
+    lib = load_library()
+    msg = lib.mmb_status_string(status).decode()
+    if status == 6:
+        msg += ": " + lib.mmb_last_cuda_error().decode()
+    raise MmbError(f"{what} failed: {msg}")
+
+
+def require_cuda():
+    import torch
+    if not torch.cuda.is_available():
+        raise MmbError("mm_masking_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+
+
+def ptr(t):
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def stream_ptr():
+    import torch
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,1131 @@
+// Weighted differentiable ICP for sm_100a: target packing, tiled brute-force nearest
+// neighbour (K3), fused residual / robust weight / Jacobian / normal-equation reduction with the
+// per-pair solve and pose update (K4+K5), result assembly, and the per-iteration adjoint sweep (K7).
+//
+// What is computed follows external/dICP/dICP/ICP.py:130-250 of the reference (see
+// include/mm_masking_b200.h and DESIGN.md for the mapping); how it is computed does not:
+//   * the (N,n,m) distance tensor of nn.py:32 is never formed -- targets stream through shared
+//     memory in bulk-async (TMA) tiles, each thread keeps R queries in registers, and a
+//     conservative fp32 filter (FADD2/FMUL2/FFMA2 + FMNMX3) sends only candidates that can
+//     still be the minimum to an exact fp64 comparison with lowest-index tie-break;
+//   * everything that is O(n) per iteration runs in fp64 regardless of the I/O dtype, so poses
+//     agree with the reference evaluated in double precision;
+//   * convergence, per-pair freezing and early exit (ICP.py:227-250) are device-side flags: the
+//     host enqueues max_iterations rounds without synchronising.
+#include "mmb_common.cuh"
+
+namespace mmb {
+
+static thread_local char g_last_cuda_error[256] = "";
+void set_last_cuda_error(cudaError_t e) {
+  const char* s = cudaGetErrorString(e);
+  int i = 0;
+  for (; s[i] && i < 255; ++i) g_last_cuda_error[i] = s[i];
+  g_last_cuda_error[i] = 0;
+}
+
+constexpr int NN_THREADS = 128;   // threads per NN block
+constexpr int NN_R = 4;           // queries per thread
+constexpr int NN_QB = NN_THREADS * NN_R;
+constexpr int NN_TILE = 1024;     // targets per shared-memory tile
+constexpr int STEP_THREADS = 512;
+constexpr int BWD_THREADS = 512;
+constexpr float PAD_COORD = __builtin_huge_valf();   // filter copy padding: never passes the filter
+
+struct IcpPlan {
+  int N, n, m, mp, R;            // mp: m rounded up to NN_TILE; R residual rows
+  int qtiles, S, tiles_per_slice;
+  int D;                         // solved DoF
+};
+
+static int pick_slices(int N, int qtiles, int tiles, int requested) {
+  if (requested > 0) return requested < tiles ? requested : tiles;
+  // Enough blocks for ~4 resident blocks on each of 148 SMs, in whole waves where possible.
+  const long long slots = 148LL * 4;
+  const long long units = (long long)N * qtiles;
+  int best = 1; double best_eff = -1.0;
+  for (int S = 1; S <= tiles && S <= 64; ++S) {
+    const int tps = (tiles + S - 1) / S;
+    const int Seff = (tiles + tps - 1) / tps;
+    if (Seff != S) continue;
+    const long long blocks = units * S;
+    const long long waves = (blocks + slots - 1) / slots;
+    // time ~ waves * tiles_per_slice ; ideal ~ units*tiles/slots
+    const double t = (double)waves * tps;
+    const double ideal = (double)units * tiles / (double)slots;
+    double eff = ideal / t;
+    if (blocks < slots) eff = (double)blocks / slots * ((double)tiles / ((double)tps * S));
+    eff -= 0.002 * S;            // partial-merge traffic grows with S
+    if (eff > best_eff) { best_eff = eff; best = S; }
+  }
+  return best;
+}
+
+static IcpPlan make_plan(int N, int n, int m, int icp_type, int dim, int nn_slices) {
+  IcpPlan pl;
+  pl.N = N; pl.n = n; pl.m = m;
+  pl.mp = (int)align_up((size_t)m, NN_TILE);
+  pl.R = icp_type == MMB_PT2PT ? 3 * n : n;
+  pl.qtiles = (n + NN_QB - 1) / NN_QB;
+  const int tiles = pl.mp / NN_TILE;
+  pl.S = pick_slices(N, pl.qtiles, tiles, nn_slices);
+  pl.tiles_per_slice = (tiles + pl.S - 1) / pl.S;
+  pl.S = (tiles + pl.tiles_per_slice - 1) / pl.tiles_per_slice;
+  pl.D = dim == 2 ? 3 : 6;
+  return pl;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Workspace / saved-state layouts
+// ---------------------------------------------------------------------------------------------
+struct IcpWorkspace {
+  float *tx, *ty, *tz;           // (N, mp) fp32 filter copy of the targets, SoA
+  double* pose;                  // (N,12) current C (row-major) and r
+  double* pd2; int* pidx;        // (S,N,n) per-slice partial minima
+  int* idx_cur;                  // (N,n) correspondences of the latest search
+  double* prev_cost;             // (N)
+  double* num_iters;             // (N) latched iteration count (0 = not latched)
+  double* match_ratio;           // (N) latched
+  int* frozen;                   // (N) prior weights zeroed (ICP.py:246-247)
+  int* conv;                     // (N)
+  int* n_matched;                // (N) rows with w > thresh in the latest iteration
+  int* n_start;                  // (N) rows with prior weight > thresh
+  int* counters;                 // [0] samples frozen, [1] done flag, [2] iterations executed
+  size_t bytes;
+};
+
+static IcpWorkspace carve_workspace(void* base, const IcpPlan& pl) {
+  Carver c(base);
+  IcpWorkspace w;
+  const size_t Nmp = (size_t)pl.N * pl.mp, Nn = (size_t)pl.N * pl.n;
+  w.tx = c.take<float>(Nmp); w.ty = c.take<float>(Nmp); w.tz = c.take<float>(Nmp);
+  w.pose = c.take<double>((size_t)pl.N * 12);
+  w.pd2 = c.take<double>((size_t)pl.S * Nn);
+  w.pidx = c.take<int>((size_t)pl.S * Nn);
+  w.idx_cur = c.take<int>(Nn);
+  w.prev_cost = c.take<double>(pl.N);
+  w.num_iters = c.take<double>(pl.N);
+  w.match_ratio = c.take<double>(pl.N);
+  w.frozen = c.take<int>(pl.N);
+  w.conv = c.take<int>(pl.N);
+  w.n_matched = c.take<int>(pl.N);
+  w.n_start = c.take<int>(pl.N);
+  w.counters = c.take<int>(8);
+  w.bytes = c.off;
+  return w;
+}
+
+struct IcpSaved {
+  int* idx_hist;       // (K,N,n)
+  double* pose_hist;   // (K,N,12) pose before iteration k
+  double* A_hist;      // (K,N,36) normal matrix (with the 1e-12 ridge), row-major DxD in the corner
+  double* delta_hist;  // (K,N,6)  solved step in the D solved slots
+  int* active;         // (K,N)    1 if the pair was updated in iteration k
+  double* pose_final;  // (N,12)
+  int* iters_done;     // (1)
+  size_t bytes;
+};
+
+static IcpSaved carve_saved(void* base, const IcpPlan& pl, int K) {
+  Carver c(base);
+  IcpSaved s;
+  s.idx_hist = c.take<int>((size_t)K * pl.N * pl.n);
+  s.pose_hist = c.take<double>((size_t)K * pl.N * 12);
+  s.A_hist = c.take<double>((size_t)K * pl.N * 36);
+  s.delta_hist = c.take<double>((size_t)K * pl.N * 6);
+  s.active = c.take<int>((size_t)K * pl.N);
+  s.pose_final = c.take<double>((size_t)pl.N * 12);
+  s.iters_done = c.take<int>(8);
+  s.bytes = c.off;
+  return s;
+}
+
+// ---------------------------------------------------------------------------------------------
+// init: pose <- T_init, flags cleared
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void init_state_kernel(const T* __restrict__ T_init, IcpWorkspace w, int N) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b == 0) { w.counters[0] = 0; w.counters[1] = 0; w.counters[2] = 0; }
+  if (b >= N) return;
+  const T* Ti = T_init + (size_t)b * 16;
+  double* P = w.pose + (size_t)b * 12;
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j) P[i * 3 + j] = (double)Ti[i * 4 + j];
+    P[9 + i] = (double)Ti[i * 4 + 3];
+  }
+  w.prev_cost[b] = 0.0; w.num_iters[b] = 0.0; w.match_ratio[b] = 0.0;
+  w.frozen[b] = 0; w.conv[b] = 0; w.n_matched[b] = 0; w.n_start[b] = 0;
+}
+
+__global__ void identity_pose_kernel(double* pose, int N) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= N) return;
+  double* P = pose + (size_t)b * 12;
+  for (int i = 0; i < 12; ++i) P[i] = 0.0;
+  P[0] = P[4] = P[8] = 1.0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// pack: AoS targets of either dtype -> fp32 SoA filter copy, padded to the tile size with +inf
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void pack_targets_kernel(const T* __restrict__ target, int cols, int N, int m, int mp, float* __restrict__ tx,
+                                    float* __restrict__ ty, float* __restrict__ tz) {
+  const size_t total = (size_t)N * mp;
+  for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(g / mp), j = (int)(g % mp);
+    float x = PAD_COORD, y = PAD_COORD, z = PAD_COORD;
+    if (j < m) {
+      const T* row = target + ((size_t)b * m + j) * cols;
+      x = (float)row[0]; y = (float)row[1]; z = (float)row[2];
+    }
+    tx[g] = x; ty[g] = y; tz[g] = z;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3: nearest neighbour
+// ---------------------------------------------------------------------------------------------
+// Filter threshold on the fp32 squared distance for an exact best squared distance D2 (fp64).
+// Derivation (DESIGN.md "NN filter"): with u = 2^-24, every fp32-evaluated d~^2 of a candidate
+// whose true distance d <= D satisfies d~^2 <= (D(1+3u) + 3u|q|_1)^2 (1+8u); we use 2^-22
+// for u (4x margin) and round up.
+__device__ __forceinline__ float filter_threshold(double D2, double qnorm1) {
+  if (!(D2 < 1.0e300)) return FLT_MAX;
+  const double u = 2.384185791015625e-07;      // 2^-22
+  const double Tb = sqrt(D2) * (1.0 + 3.0 * u) + 3.0 * u * qnorm1;
+  const double t2 = Tb * Tb * (1.0 + 8.0 * u);
+  if (t2 >= 3.0e38) return FLT_MAX;
+  return __double2float_ru(t2);
+}
+
+template <typename T, int DIM>
+__device__ __forceinline__ double exact_dist2(const T* __restrict__ row, double qx, double qy, double qz) {
+  const double dx = (double)row[0] - qx, dy = (double)row[1] - qy;
+  double d2 = fma(dy, dy, __dmul_rn(dx, dx));
+  if (DIM == 3) {
+    const double dz = (double)row[2] - qz;
+    d2 = fma(dz, dz, d2);
+  }
+  return d2;
+}
+
+struct ExactState { double D2; int I; float thr; };
+
+// Cold path of the search: candidates whose fp32 distance passed the filter are compared exactly
+// (fp64 on the caller's own coordinates), lowest index winning ties.  Kept out of line so the
+// streaming loop stays compact in the instruction cache.
+template <typename T, int DIM>
+__device__ __noinline__ ExactState exact_path(const T* __restrict__ tgt, int cols, int m, int j0, float d0, float d1,
+                                              float d2, float d3, float thr, double qx, double qy, double qz,
+                                              double qn1, double D2, int I) {
+  const float dd[4] = {d0, d1, d2, d3};
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const int j = j0 + c;
+    if (dd[c] <= thr && j < m) {
+      const double e2 = exact_dist2<T, DIM>(tgt + (size_t)j * cols, qx, qy, qz);
+      if (e2 < D2 || (e2 == D2 && j < I)) {
+        D2 = e2; I = j;
+        thr = filter_threshold(e2, qn1);
+      }
+    }
+  }
+  ExactState st; st.D2 = D2; st.I = I; st.thr = thr;
+  return st;
+}
+
+struct NNArgs {
+  const void* source;        // (N,n,3) points that are rotated/translated by pose before the search
+  const void* target;        // (N,m,cols) exact targets
+  const double* pose;        // (N,12)
+  const float *tx, *ty, *tz; // filter copy
+  const int* idx_prev;       // (N,n) warm start or nullptr
+  const int* frozen;         // (N) or nullptr
+  const int* counters;       // done flag at [1], or nullptr
+  double* pd2; int* pidx;    // (S,N,n)
+  int N, n, m, mp, cols, tiles_per_slice, S;
+};
+
+template <typename T, int DIM>
+__global__ void __launch_bounds__(NN_THREADS) nn_search_kernel(NNArgs a) {
+  const int qt = blockIdx.x, s = blockIdx.y, b = blockIdx.z;
+  if (a.counters && a.counters[1]) return;
+  if (a.frozen && a.frozen[b]) return;
+
+  __shared__ __align__(128) float sx[2][NN_TILE];
+  __shared__ __align__(128) float sy[2][NN_TILE];
+  __shared__ __align__(128) float sz[2][DIM == 3 ? NN_TILE : 4];
+  __shared__ __align__(8) uint64_t bar[2];
+  __shared__ double sC[12];
+
+  const int tid = threadIdx.x;
+  if (tid < 12) sC[tid] = a.pose[(size_t)b * 12 + tid];
+  if (tid == 0) { mbar_init(&bar[0], 1); mbar_init(&bar[1], 1); mbar_fence_init(); }
+  __syncthreads();
+
+  const int tile0 = s * a.tiles_per_slice;
+  int ntiles = a.mp / NN_TILE - tile0;
+  if (ntiles > a.tiles_per_slice) ntiles = a.tiles_per_slice;
+  const size_t tbase = (size_t)b * a.mp;
+  constexpr uint32_t kTileBytes = NN_TILE * sizeof(float);
+
+  auto issue = [&](int k) {
+    const int buf = k & 1;
+    const size_t off = tbase + (size_t)(tile0 + k) * NN_TILE;
+    mbar_expect_tx(&bar[buf], kTileBytes * DIM);
+    bulk_g2s(sx[buf], a.tx + off, kTileBytes, &bar[buf]);
+    bulk_g2s(sy[buf], a.ty + off, kTileBytes, &bar[buf]);
+    if (DIM == 3) bulk_g2s(sz[buf], a.tz + off, kTileBytes, &bar[buf]);
+  };
+  if (tid == 0 && ntiles > 0) issue(0);
+
+  // ---- per-thread queries -------------------------------------------------------------------
+  const T* src = static_cast<const T*>(a.source) + (size_t)b * a.n * 3;
+  const T* tgt = static_cast<const T*>(a.target) + (size_t)b * a.m * a.cols;
+  double qx[NN_R], qy[NN_R], qz[NN_R], qn1[NN_R], D2[NN_R];
+  float fx[NN_R], fy[NN_R], fz[NN_R], thr[NN_R];
+  int I[NN_R];
+#pragma unroll
+  for (int r = 0; r < NN_R; ++r) {
+    const int qi = qt * NN_QB + r * NN_THREADS + tid;
+    qx[r] = qy[r] = qz[r] = 0.0; qn1[r] = 0.0; D2[r] = 1.0e308; I[r] = INT_MAX;
+    thr[r] = -1.0f;                      // lanes past n never reach the exact path
+    if (qi < a.n) {
+      const double px = (double)src[(size_t)qi * 3 + 0], py = (double)src[(size_t)qi * 3 + 1];
+      const double pz = DIM == 3 ? (double)src[(size_t)qi * 3 + 2] : 0.0;
+      double ax, ay, az;
+      rotate_point(sC, px, py, pz, ax, ay, az);
+      qx[r] = __dadd_rn(ax, sC[9]); qy[r] = __dadd_rn(ay, sC[10]); qz[r] = __dadd_rn(az, sC[11]);
+      qn1[r] = fabs(qx[r]) + fabs(qy[r]) + (DIM == 3 ? fabs(qz[r]) : 0.0);
+      if (a.idx_prev) {
+        int j0 = a.idx_prev[(size_t)b * a.n + qi];
+        if (j0 >= 0 && j0 < a.m) D2[r] = exact_dist2<T, DIM>(tgt + (size_t)j0 * a.cols, qx[r], qy[r], qz[r]);
+      }
+      thr[r] = filter_threshold(D2[r], qn1[r]);
+    }
+    fx[r] = -(float)qx[r]; fy[r] = -(float)qy[r]; fz[r] = -(float)qz[r];
+  }
+
+  // ---- stream the target slice ----------------------------------------------------------------
+  for (int k = 0; k < ntiles; ++k) {
+    const int buf = k & 1;
+    if (tid == 0 && k + 1 < ntiles) issue(k + 1);
+    mbar_wait(&bar[buf], (k >> 1) & 1);
+    const float4* X = reinterpret_cast<const float4*>(sx[buf]);
+    const float4* Y = reinterpret_cast<const float4*>(sy[buf]);
+    const float4* Z = reinterpret_cast<const float4*>(sz[buf]);
+    const int jbase = (tile0 + k) * NN_TILE;
+#pragma unroll 2
+    for (int g = 0; g < NN_TILE / 4; ++g) {
+      const float4 x4 = X[g], y4 = Y[g];
+      const f32x2 xa = pack2(x4.x, x4.y), xb = pack2(x4.z, x4.w);
+      const f32x2 ya = pack2(y4.x, y4.y), yb = pack2(y4.z, y4.w);
+      f32x2 za = 0, zb = 0;
+      if (DIM == 3) { const float4 z4 = Z[g]; za = pack2(z4.x, z4.y); zb = pack2(z4.z, z4.w); }
+#pragma unroll
+      for (int r = 0; r < NN_R; ++r) {
+        const f32x2 nqx = pack2(fx[r], fx[r]), nqy = pack2(fy[r], fy[r]);
+        const f32x2 dxa = add2(xa, nqx), dxb = add2(xb, nqx);
+        const f32x2 dya = add2(ya, nqy), dyb = add2(yb, nqy);
+        f32x2 sa = fma2(dya, dya, mul2(dxa, dxa)), sb = fma2(dyb, dyb, mul2(dxb, dxb));
+        if (DIM == 3) {
+          const f32x2 nqz = pack2(fz[r], fz[r]);
+          const f32x2 dza = add2(za, nqz), dzb = add2(zb, nqz);
+          sa = fma2(dza, dza, sa); sb = fma2(dzb, dzb, sb);
+        }
+        float d0, d1, d2, d3;
+        unpack2(sa, d0, d1); unpack2(sb, d2, d3);
+        const float mn = fminf(min3(d0, d1, d2), d3);
+        if (__builtin_expect(mn <= thr[r], 0)) {
+          // exact path: rare (record-setting candidates and genuine near-ties only)
+          const ExactState st = exact_path<T, DIM>(tgt, a.cols, a.m, jbase + g * 4, d0, d1, d2, d3, thr[r], qx[r],
+                                                   qy[r], qz[r], qn1[r], D2[r], I[r]);
+          D2[r] = st.D2; I[r] = st.I; thr[r] = st.thr;
+        }
+      }
+    }
+    __syncthreads();     // everyone is done with buf before it is refilled two tiles later
+  }
+
+#pragma unroll
+  for (int r = 0; r < NN_R; ++r) {
+    const int qi = qt * NN_QB + r * NN_THREADS + tid;
+    if (qi < a.n) {
+      const size_t o = ((size_t)s * a.N + b) * a.n + qi;
+      a.pd2[o] = D2[r]; a.pidx[o] = I[r];
+    }
+  }
+}
+
+// merge the per-slice partial minima of one query (lexicographic on (d2, idx))
+__device__ __forceinline__ int merge_partials(const double* pd2, const int* pidx, int S, size_t stride, size_t o) {
+  double best = pd2[o]; int bi = pidx[o];
+  for (int s = 1; s < S; ++s) {
+    const double d = pd2[o + s * stride]; const int j = pidx[o + s * stride];
+    if (d < best || (d == best && j < bi)) { best = d; bi = j; }
+  }
+  return bi == INT_MAX ? 0 : bi;
+}
+
+__global__ void merge_only_kernel(const double* pd2, const int* pidx, int S, int N, int n, int* idx_out) {
+  const size_t total = (size_t)N * n;
+  const size_t o = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (o < total) idx_out[o] = merge_partials(pd2, pidx, S, total, o);
+}
+
+// ---------------------------------------------------------------------------------------------
+// per-row residual model shared by the forward step and the adjoint sweep
+// ---------------------------------------------------------------------------------------------
+struct RowParams {
+  int differentiable, use_trim, loss_kind;
+  double trim_dist, loss_metric, steep;
+};
+
+// weight of one residual row: w = w0 * trim(rho) * loss(e); also returns the two factors.
+__device__ __forceinline__ void row_weight(const RowParams& rp, double w0, double rho, double e, double& tw,
+                                           double& lw, double& w) {
+  tw = 1.0; lw = 1.0;
+  if (rp.use_trim) {
+    if (rp.differentiable) tw = 0.5 * tanh(rp.steep * (rp.trim_dist - rho) - 3.0) + 0.5;   // loss.py:52
+    else tw = rho > rp.trim_dist ? 0.0 : 1.0;                                              // loss.py:56
+  }
+  if (rp.loss_kind == MMB_LOSS_CAUCHY) {
+    const double q = e / rp.loss_metric;
+    lw = 1.0 / (1.0 + q * q);                                                               // loss.py:38
+  } else if (rp.loss_kind == MMB_LOSS_HUBER) {
+    const double dl = rp.loss_metric;
+    if (rp.differentiable) lw = dl * dl / (dl * dl + e * e);                                // loss.py:27
+    else lw = fabs(e) > dl ? dl / fabs(e) : 1.0;                                            // loss.py:30
+  }
+  w = w0 * tw * lw;
+}
+
+// d tw / d rho and d lw / d e
+__device__ __forceinline__ void row_weight_grad(const RowParams& rp, double rho, double e, double lw, double& dtw,
+                                                double& dlw) {
+  dtw = 0.0; dlw = 0.0;
+  if (rp.use_trim && rp.differentiable) {
+    const double th = tanh(rp.steep * (rp.trim_dist - rho) - 3.0);
+    dtw = -0.5 * rp.steep * (1.0 - th * th);
+  }
+  if (rp.loss_kind == MMB_LOSS_CAUCHY) {
+    dlw = -2.0 * e / (rp.loss_metric * rp.loss_metric) * lw * lw;
+  } else if (rp.loss_kind == MMB_LOSS_HUBER) {
+    const double dl = rp.loss_metric;
+    if (rp.differentiable) dlw = -2.0 * e / (dl * dl) * lw * lw;
+    else dlw = fabs(e) > dl ? -dl * (e > 0 ? 1.0 : -1.0) / (e * e) : 0.0;
+  }
+}
+
+template <int DIM> struct Dof { static constexpr int D = DIM == 2 ? 3 : 6; };
+// slot of solved unknown i in the 6-vector (phi_x,phi_y,phi_z,r_x,r_y,r_z): ICP.py:176-179,194-197
+template <int DIM> __device__ __forceinline__ int dof_slot(int i) { return DIM == 2 ? i + 2 : i; }
+
+struct StepArgs {
+  const void* source; const void* target; const void* weight;   // weight may be null
+  IcpWorkspace w; IcpSaved sv;
+  void* deltas; void* weights_hist; void* costs;
+  RowParams rp;
+  int N, n, m, cols, S, K, it, const_iter, save, has_weight;
+  double tol, match_thresh;
+};
+
+// ---------------------------------------------------------------------------------------------
+// K4 + K5: one block per pair and iteration
+// ---------------------------------------------------------------------------------------------
+template <typename T, int ICP, int DIM>
+__global__ void __launch_bounds__(STEP_THREADS) icp_step_kernel(StepArgs a) {
+  constexpr int D = Dof<DIM>::D;
+  constexpr int NA = D * (D + 1) / 2;
+  constexpr int NV = NA + D + 4;     // A (upper), g, cost, sum w, matched, at-start
+  constexpr int ROWS = ICP == MMB_PT2PT ? 3 : 1;
+  __shared__ double scratch[NV * (STEP_THREADS / 32 + 1)];
+  __shared__ double sP[12];
+  __shared__ int s_flag;
+
+  const int b = blockIdx.x, tid = threadIdx.x, it = a.it;
+  if (a.w.counters[1]) return;                      // every pair converged earlier (ICP.py:249-250)
+  const int R = a.n * ROWS;
+  T* wh = static_cast<T*>(a.weights_hist) + ((size_t)b * a.K + it) * R;
+  T* dl = static_cast<T*>(a.deltas) + ((size_t)b * a.K + it) * 6;
+  T* cs = static_cast<T*>(a.costs) + (size_t)b * a.K + it;
+
+  if (a.w.frozen[b]) {
+    // Prior weights are zero: w_sqrt = sqrt(1e-10) - 1e-5 == 0 exactly, so A = 1e-12 I, g = 0 and
+    // the step is 0; the histories repeat the previous entries (ICP.py:215-224).
+    for (int i = tid; i < R; i += blockDim.x) wh[i] = it > 0 ? wh[i - (ptrdiff_t)R] : (T)0;
+    if (tid < 6) dl[tid] = (T)0;
+    if (tid == 0) {
+      *cs = from_double<T>(a.w.prev_cost[b]);
+      a.w.n_matched[b] = 0;
+      if (a.save) a.sv.active[(size_t)it * a.N + b] = 0;
+    }
+    return;
+  }
+
+  if (tid < 12) sP[tid] = a.w.pose[(size_t)b * 12 + tid];
+  __syncthreads();
+
+  const T* src = static_cast<const T*>(a.source) + (size_t)b * a.n * 3;
+  const T* tgt = static_cast<const T*>(a.target) + (size_t)b * a.m * a.cols;
+  const T* wgt = a.has_weight ? static_cast<const T*>(a.weight) + (size_t)b * a.n : nullptr;
+  const size_t stride = (size_t)a.N * a.n;
+
+  double acc[NV];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) acc[k] = 0.0;
+
+  for (int i = tid; i < a.n; i += blockDim.x) {
+    const size_t o = (size_t)b * a.n + i;
+    const int j = merge_partials(a.w.pd2, a.w.pidx, a.S, stride, o);
+    a.w.idx_cur[o] = j;
+    if (a.save) a.sv.idx_hist[(size_t)it * stride + o] = j;
+
+    const double px = (double)src[i * 3 + 0], py = (double)src[i * 3 + 1];
+    const double pz = DIM == 3 ? (double)src[i * 3 + 2] : 0.0;
+    double ax, ay, az;
+    rotate_point(sP, px, py, pz, ax, ay, az);
+    const double yx = __dadd_rn(ax, sP[9]), yy = __dadd_rn(ay, sP[10]), yz = __dadd_rn(az, sP[11]);
+    const T* row = tgt + (size_t)j * a.cols;
+    const double dx = yx - (double)row[0], dy = yy - (double)row[1];
+    const double dz = yz - (DIM == 3 ? (double)row[2] : 0.0);
+    const double w0 = wgt ? (double)wgt[i] : 1.0;
+
+    double j6[ROWS][6], e[ROWS], rho[ROWS];
+    if (ICP == MMB_PT2PL) {
+      const double nx = (double)row[3], ny = (double)row[4], nz = DIM == 3 ? (double)row[5] : 0.0;
+      e[0] = dx * nx + dy * ny + dz * nz;                            // ICP.py:145
+      rho[0] = sqrt(dx * dx + dy * dy + dz * dz);
+      j6[0][0] = ny * az - nz * ay; j6[0][1] = nz * ax - nx * az; j6[0][2] = nx * ay - ny * ax;   // n x a
+      j6[0][3] = -nx; j6[0][4] = -ny; j6[0][5] = -nz;               // ICP.py:165-166
+    } else {
+      const double dd[3] = {dx, dy, dz};
+      const double sk[3][3] = {{0.0, -az, ay}, {az, 0.0, -ax}, {-ay, ax, 0.0}};
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        e[c] = dd[c]; rho[c] = fabs(dd[c]);                          // ICP.py:147, loss.py:45-52
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { j6[c][k] = sk[c][k]; j6[c][3 + k] = (c == k) ? -1.0 : 0.0; }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < ROWS; ++c) {
+      double tw, lw, w;
+      row_weight(a.rp, w0, rho[c], e[c], tw, lw, w);
+      wh[i * ROWS + c] = from_double<T>(w);
+      const double ws = sqrt(w + 1.0e-10) - 1.0e-5;                  // ICP.py:184
+      const double s2 = ws * ws;
+      double jv[D];
+#pragma unroll
+      for (int k = 0; k < D; ++k) jv[k] = j6[c][DIM == 2 ? k + 2 : k];
+      int q = 0;
+#pragma unroll
+      for (int r0 = 0; r0 < D; ++r0) {
+#pragma unroll
+        for (int c0 = r0; c0 < D; ++c0) acc[q++] += s2 * jv[r0] * jv[c0];
+      }
+#pragma unroll
+      for (int k = 0; k < D; ++k) acc[NA + k] += s2 * jv[k] * e[c];
+      acc[NA + D + 0] += s2 * e[c] * e[c];
+      acc[NA + D + 1] += w;
+      acc[NA + D + 2] += (w > a.match_thresh) ? 1.0 : 0.0;
+      acc[NA + D + 3] += (w0 > a.match_thresh) ? 1.0 : 0.0;
+    }
+  }
+
+  const double* tot = block_sum<NV>(acc, scratch);
+
+  if (tid == 0) {
+    double A[D * D], g[D], x[D];
+    int q = 0;
+    for (int r0 = 0; r0 < D; ++r0)
+      for (int c0 = r0; c0 < D; ++c0) { A[r0 * D + c0] = tot[q]; A[c0 * D + r0] = tot[q]; ++q; }
+    for (int k = 0; k < D; ++k) { A[k * D + k] += 1e-12; g[k] = tot[NA + k]; }      // ICP.py:190
+    solve_spd<D>(A, g, x);
+    double d6[6] = {0, 0, 0, 0, 0, 0};
+    for (int k = 0; k < D; ++k) d6[dof_slot<DIM>(k)] = -x[k];                       // ICP.py:191-197
+
+    if (a.save) {
+      double* Ps = a.sv.pose_hist + ((size_t)it * a.N + b) * 12;
+      for (int k = 0; k < 12; ++k) Ps[k] = sP[k];
+      double* As = a.sv.A_hist + ((size_t)it * a.N + b) * 36;
+      for (int k = 0; k < D * D; ++k) As[k] = A[k];
+      double* Ds = a.sv.delta_hist + ((size_t)it * a.N + b) * 6;
+      for (int k = 0; k < 6; ++k) Ds[k] = d6[k];
+      a.sv.active[(size_t)it * a.N + b] = 1;
+    }
+
+    // pose update: C <- exp(dphi^)^T C ; r <- r - dr   (ICP.py:200-207)
+    double dC[9], Cn[9];
+    so3_exp(d6, dC);
+    for (int i = 0; i < 3; ++i)
+      for (int jx = 0; jx < 3; ++jx) {
+        double s = 0.0;
+        for (int k = 0; k < 3; ++k) s += dC[k * 3 + i] * sP[k * 3 + jx];
+        Cn[i * 3 + jx] = s;
+      }
+    double* P = a.w.pose + (size_t)b * 12;
+    for (int k = 0; k < 9; ++k) P[k] = Cn[k];
+    for (int k = 0; k < 3; ++k) P[9 + k] = sP[9 + k] - d6[3 + k];
+
+    for (int k = 0; k < 6; ++k) dl[k] = from_double<T>(d6[k]);
+    double cost = tot[NA + D + 0];
+    if (cost == 0.0 && it > 0) cost = a.w.prev_cost[b];                             // ICP.py:220-222
+    a.w.prev_cost[b] = cost;
+    *cs = from_double<T>(cost);
+
+    const int matched = (int)(tot[NA + D + 2] + 0.5), at_start = (int)(tot[NA + D + 3] + 0.5);
+    a.w.n_matched[b] = matched;
+    a.w.n_start[b] = at_start;
+    double nrm = 0.0;
+    for (int k = 0; k < 6; ++k) nrm += d6[k] * d6[k];
+    nrm = sqrt(nrm);
+    // the reference compares in the tensors' dtype
+    const bool small = sizeof(T) == 4 ? ((float)nrm < (float)a.tol) : (nrm < a.tol);
+    if (small) {
+      a.w.conv[b] = 1;
+      if (!a.const_iter) {                                                          // ICP.py:230-247
+        if (a.w.num_iters[b] == 0.0) a.w.num_iters[b] = (double)(it + 1);
+        if (a.w.match_ratio[b] == 0.0) a.w.match_ratio[b] = (double)matched / (double)(at_start > 0 ? at_start : 1);
+        a.w.frozen[b] = 1;
+        const int nf = atomicAdd(&a.w.counters[0], 1) + 1;
+        if (nf == a.N) a.w.counters[1] = 1;
+      }
+    }
+    a.w.counters[2] = it + 1;
+    s_flag = (tot[NA + D + 1] == 0.0 && it > 0) ? 1 : 0;
+  }
+  __syncthreads();
+  if (s_flag) {                        // all weights zero: repeat the previous row (ICP.py:215-218)
+    for (int i = tid; i < R; i += blockDim.x) wh[i] = wh[i - (ptrdiff_t)R];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// finish: aligned cloud, T, stats
+// ---------------------------------------------------------------------------------------------
+template <typename T, int DIM>
+__global__ void icp_finish_kernel(const T* __restrict__ source, IcpWorkspace w, IcpSaved sv, int save, int N, int n,
+                                  T* __restrict__ T_out, T* __restrict__ pc_out, uint8_t* converged, T* iterations,
+                                  T* matched_ratio, int32_t* iters_done) {
+  const int b = blockIdx.x, tid = threadIdx.x;
+  __shared__ double sP[12];
+  if (tid < 12) sP[tid] = w.pose[(size_t)b * 12 + tid];
+  __syncthreads();
+  const T* src = source + (size_t)b * n * 3;
+  T* pc = pc_out + (size_t)b * n * 3;
+  for (int i = tid; i < n; i += blockDim.x) {
+    const double px = (double)src[i * 3 + 0], py = (double)src[i * 3 + 1];
+    const double pz = DIM == 3 ? (double)src[i * 3 + 2] : 0.0;
+    double ax, ay, az;
+    rotate_point(sP, px, py, pz, ax, ay, az);
+    pc[i * 3 + 0] = from_double<T>(ax + sP[9]);
+    pc[i * 3 + 1] = from_double<T>(ay + sP[10]);
+    pc[i * 3 + 2] = from_double<T>(az + sP[11]);
+  }
+  if (tid == 0) {
+    T* To = T_out + (size_t)b * 16;
+    for (int i = 0; i < 3; ++i) {
+      for (int j = 0; j < 3; ++j) To[i * 4 + j] = from_double<T>(sP[i * 3 + j]);
+      To[i * 4 + 3] = from_double<T>(sP[9 + i]);
+    }
+    To[12] = To[13] = To[14] = (T)0; To[15] = (T)1;
+    const int done = w.counters[2];
+    converged[b] = (uint8_t)w.conv[b];
+    const double ni = w.num_iters[b];
+    iterations[b] = from_double<T>(ni == 0.0 ? (double)done : ni);                  // ICP.py:257
+    double mr = w.match_ratio[b];
+    if (mr == 0.0) {                                                                // ICP.py:258-261
+      const int at_start = w.frozen[b] ? 0 : w.n_start[b];
+      mr = (double)w.n_matched[b] / (double)(at_start > 0 ? at_start : 1);
+    }
+    matched_ratio[b] = from_double<T>(mr);
+    if (b == 0) *iters_done = done;
+    if (save) {
+      for (int k = 0; k < 12; ++k) sv.pose_final[(size_t)b * 12 + k] = sP[k];
+      if (b == 0) sv.iters_done[0] = done;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K7: adjoint sweep, one block per pair, iterations in reverse
+// ---------------------------------------------------------------------------------------------
+struct BwdArgs {
+  const void* source; const void* target; const void* weight;
+  IcpSaved sv;
+  const void* grad_T; const void* grad_pc;
+  void* grad_source; void* grad_target; void* grad_T_init; void* grad_weight;
+  RowParams rp;
+  int N, n, m, cols, K, has_weight;
+};
+
+template <typename T> __device__ __forceinline__ void atomic_add_t(T* p, double v) { atomicAdd(p, from_double<T>(v)); }
+
+template <typename T, int ICP, int DIM>
+__global__ void __launch_bounds__(BWD_THREADS) icp_backward_kernel(BwdArgs a) {
+  constexpr int D = Dof<DIM>::D;
+  __shared__ double scratch[12 * (BWD_THREADS / 32 + 1)];
+  __shared__ double sP[12], sCb[9], sRb[3], sLam[6], sDel[6];
+  __shared__ int s_active;
+
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const T* src = static_cast<const T*>(a.source) + (size_t)b * a.n * 3;
+  const T* tgt = static_cast<const T*>(a.target) + (size_t)b * a.m * a.cols;
+  const T* wgt = a.has_weight ? static_cast<const T*>(a.weight) + (size_t)b * a.n : nullptr;
+  const T* gT = a.grad_T ? static_cast<const T*>(a.grad_T) + (size_t)b * 16 : nullptr;
+  const T* gpc = a.grad_pc ? static_cast<const T*>(a.grad_pc) + (size_t)b * a.n * 3 : nullptr;
+  T* gsrc = a.grad_source ? static_cast<T*>(a.grad_source) + (size_t)b * a.n * 3 : nullptr;
+  T* gtgt = a.grad_target ? static_cast<T*>(a.grad_target) + (size_t)b * a.m * a.cols : nullptr;
+  T* gw = a.grad_weight ? static_cast<T*>(a.grad_weight) + (size_t)b * a.n : nullptr;
+  const int iters = a.sv.iters_done[0];
+  const size_t stride = (size_t)a.N * a.n;
+
+  // ---- adjoint of the outputs: pc = C_K p + r_K and T = [C_K r_K] ------------------------------
+  if (tid < 12) sP[tid] = a.sv.pose_final[(size_t)b * 12 + tid];
+  __syncthreads();
+  {
+    double acc[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) acc[k] = 0.0;
+    for (int i = tid; i < a.n; i += blockDim.x) {
+      double g0 = 0, g1 = 0, g2 = 0;
+      if (gpc) { g0 = (double)gpc[i * 3]; g1 = (double)gpc[i * 3 + 1]; g2 = (double)gpc[i * 3 + 2]; }
+      const double px = (double)src[i * 3], py = (double)src[i * 3 + 1], pz = DIM == 3 ? (double)src[i * 3 + 2] : 0.0;
+      acc[0] += g0 * px; acc[1] += g0 * py; acc[2] += g0 * pz;
+      acc[3] += g1 * px; acc[4] += g1 * py; acc[5] += g1 * pz;
+      acc[6] += g2 * px; acc[7] += g2 * py; acc[8] += g2 * pz;
+      acc[9] += g0; acc[10] += g1; acc[11] += g2;
+      if (gsrc) {
+        gsrc[i * 3 + 0] = from_double<T>(sP[0] * g0 + sP[3] * g1 + sP[6] * g2);
+        gsrc[i * 3 + 1] = from_double<T>(sP[1] * g0 + sP[4] * g1 + sP[7] * g2);
+        gsrc[i * 3 + 2] = DIM == 3 ? from_double<T>(sP[2] * g0 + sP[5] * g1 + sP[8] * g2) : (T)0;
+      }
+      if (gw) gw[i] = (T)0;
+    }
+    const double* tot = block_sum<12>(acc, scratch);
+    if (tid < 9) sCb[tid] = tot[tid] + (gT ? (double)gT[(tid / 3) * 4 + (tid % 3)] : 0.0);
+    if (tid < 3) sRb[tid] = tot[9 + tid] + (gT ? (double)gT[tid * 4 + 3] : 0.0);
+    __syncthreads();
+  }
+
+  for (int k = iters - 1; k >= 0; --k) {
+    if (tid == 0) s_active = a.sv.active[(size_t)k * a.N + b];
+    __syncthreads();
+    if (!s_active) { __syncthreads(); continue; }       // frozen pair: the iteration is the identity
+    if (tid < 12) sP[tid] = a.sv.pose_hist[((size_t)k * a.N + b) * 12 + tid];
+    if (tid < 6) sDel[tid] = a.sv.delta_hist[((size_t)k * a.N + b) * 6 + tid];
+    __syncthreads();
+    if (tid == 0) {
+      // C_{k+1} = dC^T C_k, r_{k+1} = r_k - dr, dC = exp(dphi^)
+      double dC[9], dCb[9], Cb_old[9], G[9], sv3[3], phib[3];
+      so3_exp(sDel, dC);
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+          double s1 = 0.0, s2 = 0.0;
+          for (int q = 0; q < 3; ++q) {
+            s1 += sP[i * 3 + q] * sCb[j * 3 + q];        // dCbar = C_k Cbar_{k+1}^T
+            s2 += dC[i * 3 + q] * sCb[q * 3 + j];        // Cbar_k (part) = dC Cbar_{k+1}
+          }
+          dCb[i * 3 + j] = s1; Cb_old[i * 3 + j] = s2;
+        }
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+          double s = 0.0;
+          for (int q = 0; q < 3; ++q) s += dCb[i * 3 + q] * dC[j * 3 + q];   // G = dCbar dC^T
+          G[i * 3 + j] = s;
+        }
+      sv3[0] = G[7] - G[5]; sv3[1] = G[2] - G[6]; sv3[2] = G[3] - G[1];
+      so3_left_jacobian_T_apply(sDel, sv3, phib);
+      double d6b[6] = {phib[0], phib[1], phib[2], -sRb[0], -sRb[1], -sRb[2]};
+      double db[D], lam[D], A[D * D];
+      for (int q = 0; q < D; ++q) db[q] = d6b[dof_slot<DIM>(q)];
+      const double* As = a.sv.A_hist + ((size_t)k * a.N + b) * 36;
+      for (int q = 0; q < D * D; ++q) A[q] = As[q];
+      solve_spd<D>(A, db, lam);
+      // lambda = A^-1 deltabar on the solved slots
+      for (int q = 0; q < 6; ++q) sLam[q] = 0.0;
+      for (int q = 0; q < D; ++q) sLam[dof_slot<DIM>(q)] = lam[q];
+      for (int q = 0; q < 9; ++q) sCb[q] = Cb_old[q];
+    }
+    __syncthreads();
+
+    // delta = -A^-1 g with A = sum s j j^T, g = sum s j e, s = w_sqrt^2.  Then gbar = -lambda and
+    // Abar = -lambda delta^T, so with alpha = lambda.j and beta = delta.j + e every row has
+    //   sbar = -alpha beta,  ebar = -s alpha,  jbar = -s (lambda beta + delta alpha).
+    double acc[12];
+#pragma unroll
+    for (int q = 0; q < 12; ++q) acc[q] = 0.0;
+    for (int i = tid; i < a.n; i += blockDim.x) {
+      const int j = a.sv.idx_hist[(size_t)k * stride + (size_t)b * a.n + i];
+      const double px = (double)src[i * 3], py = (double)src[i * 3 + 1], pz = DIM == 3 ? (double)src[i * 3 + 2] : 0.0;
+      double ax, ay, az;
+      rotate_point(sP, px, py, pz, ax, ay, az);
+      const double yx = __dadd_rn(ax, sP[9]), yy = __dadd_rn(ay, sP[10]), yz = __dadd_rn(az, sP[11]);
+      const T* row = tgt + (size_t)j * a.cols;
+      const double dv[3] = {yx - (double)row[0], yy - (double)row[1], yz - (DIM == 3 ? (double)row[2] : 0.0)};
+      const double w0 = wgt ? (double)wgt[i] : 1.0;
+      double ab[3] = {0, 0, 0}, dbar[3] = {0, 0, 0}, nb[3] = {0, 0, 0}, w0b = 0.0;
+
+      if (ICP == MMB_PT2PL) {
+        const double nv[3] = {(double)row[3], (double)row[4], DIM == 3 ? (double)row[5] : 0.0};
+        const double e = dv[0] * nv[0] + dv[1] * nv[1] + dv[2] * nv[2];
+        const double rho = sqrt(dv[0] * dv[0] + dv[1] * dv[1] + dv[2] * dv[2]);
+        double j6[6];
+        j6[0] = nv[1] * az - nv[2] * ay; j6[1] = nv[2] * ax - nv[0] * az; j6[2] = nv[0] * ay - nv[1] * ax;
+        j6[3] = -nv[0]; j6[4] = -nv[1]; j6[5] = -nv[2];
+        double tw, lw, w;
+        row_weight(a.rp, w0, rho, e, tw, lw, w);
+        const double root = sqrt(w + 1.0e-10), ws = root - 1.0e-5, s2 = ws * ws;
+        double alpha = 0.0, beta = e;
+#pragma unroll
+        for (int q = 0; q < D; ++q) { const int sl = DIM == 2 ? q + 2 : q; alpha += sLam[sl] * j6[sl]; beta += sDel[sl] * j6[sl]; }
+        const double sbar = -alpha * beta;
+        double ebar = -s2 * alpha;
+        double jb[6] = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int q = 0; q < D; ++q) { const int sl = DIM == 2 ? q + 2 : q; jb[sl] = -s2 * (sLam[sl] * beta + sDel[sl] * alpha); }
+        const double wbar = sbar * ws / root;
+        w0b = wbar * tw * lw;
+        double dtw, dlw;
+        row_weight_grad(a.rp, rho, e, lw, dtw, dlw);
+        ebar += wbar * w0 * tw * dlw;
+        const double rhob = wbar * w0 * lw * dtw;
+        if (rho > 0.0) { dbar[0] = rhob * dv[0] / rho; dbar[1] = rhob * dv[1] / rho; dbar[2] = rhob * dv[2] / rho; }
+#pragma unroll
+        for (int q = 0; q < 3; ++q) { dbar[q] += ebar * nv[q]; nb[q] = ebar * dv[q] - jb[3 + q]; }
+        // J_C = n x a : nbar += a x jbC ; abar = jbC x n
+        nb[0] += ay * jb[2] - az * jb[1]; nb[1] += az * jb[0] - ax * jb[2]; nb[2] += ax * jb[1] - ay * jb[0];
+        ab[0] = jb[1] * nv[2] - jb[2] * nv[1]; ab[1] = jb[2] * nv[0] - jb[0] * nv[2]; ab[2] = jb[0] * nv[1] - jb[1] * nv[0];
+      } else {
+        const double sk[3][3] = {{0.0, -az, ay}, {az, 0.0, -ax}, {-ay, ax, 0.0}};
+        double Sb[3][3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          const double e = dv[c], rho = fabs(dv[c]);
+          double j6[6];
+#pragma unroll
+          for (int q = 0; q < 3; ++q) { j6[q] = sk[c][q]; j6[3 + q] = (c == q) ? -1.0 : 0.0; }
+          double tw, lw, w;
+          row_weight(a.rp, w0, rho, e, tw, lw, w);
+          const double root = sqrt(w + 1.0e-10), ws = root - 1.0e-5, s2 = ws * ws;
+          double alpha = 0.0, beta = e;
+#pragma unroll
+          for (int q = 0; q < D; ++q) { const int sl = DIM == 2 ? q + 2 : q; alpha += sLam[sl] * j6[sl]; beta += sDel[sl] * j6[sl]; }
+          const double sbar = -alpha * beta;
+          double ebar = -s2 * alpha;
+          const double wbar = sbar * ws / root;
+          w0b += wbar * tw * lw;
+          double dtw, dlw;
+          row_weight_grad(a.rp, rho, e, lw, dtw, dlw);
+          ebar += wbar * w0 * tw * dlw;
+          const double rhob = wbar * w0 * lw * dtw;
+          dbar[c] = ebar + rhob * (dv[c] > 0.0 ? 1.0 : (dv[c] < 0.0 ? -1.0 : 0.0));
+#pragma unroll
+          for (int q = 0; q < 3; ++q) {
+            const bool solved = DIM == 3 || q == 2;
+            Sb[c][q] = solved ? -s2 * (sLam[q] * beta + sDel[q] * alpha) : 0.0;
+          }
+        }
+        ab[0] = Sb[2][1] - Sb[1][2]; ab[1] = Sb[0][2] - Sb[2][0]; ab[2] = Sb[1][0] - Sb[0][1];
+      }
+      // d = a + r - q ; a = C p
+#pragma unroll
+      for (int q = 0; q < 3; ++q) ab[q] += dbar[q];
+      acc[0] += ab[0] * px; acc[1] += ab[0] * py; acc[2] += ab[0] * pz;
+      acc[3] += ab[1] * px; acc[4] += ab[1] * py; acc[5] += ab[1] * pz;
+      acc[6] += ab[2] * px; acc[7] += ab[2] * py; acc[8] += ab[2] * pz;
+      acc[9] += dbar[0]; acc[10] += dbar[1]; acc[11] += dbar[2];
+      if (gsrc) {
+        gsrc[i * 3 + 0] += from_double<T>(sP[0] * ab[0] + sP[3] * ab[1] + sP[6] * ab[2]);
+        gsrc[i * 3 + 1] += from_double<T>(sP[1] * ab[0] + sP[4] * ab[1] + sP[7] * ab[2]);
+        if (DIM == 3) gsrc[i * 3 + 2] += from_double<T>(sP[2] * ab[0] + sP[5] * ab[1] + sP[8] * ab[2]);
+      }
+      if (gw) gw[i] += from_double<T>(w0b);
+      if (gtgt) {
+        T* grow = gtgt + (size_t)j * a.cols;
+        atomic_add_t(grow + 0, -dbar[0]); atomic_add_t(grow + 1, -dbar[1]);
+        if (DIM == 3) atomic_add_t(grow + 2, -dbar[2]);
+        if (ICP == MMB_PT2PL) {
+          atomic_add_t(grow + 3, nb[0]); atomic_add_t(grow + 4, nb[1]);
+          if (DIM == 3) atomic_add_t(grow + 5, nb[2]);
+        }
+      }
+    }
+    const double* tot = block_sum<12>(acc, scratch);
+    if (tid < 9) sCb[tid] += tot[tid];
+    if (tid < 3) sRb[tid] += tot[9 + tid];
+    __syncthreads();
+  }
+
+  if (a.grad_T_init && tid < 16) {
+    T* g = static_cast<T*>(a.grad_T_init) + (size_t)b * 16;
+    const int i = tid / 4, j = tid % 4;
+    double v = 0.0;
+    if (i < 3) v = j < 3 ? sCb[i * 3 + j] : sRb[i];
+    g[tid] = from_double<T>(v);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// FP32 FMA-pipe probe (roofline denominator for the NN filter)
+// ---------------------------------------------------------------------------------------------
+__global__ void fp32_probe_kernel(int iters, int packed, float* out) {
+  float seed = 1.0f + 1e-6f * threadIdx.x;
+  if (!packed) {
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = seed + k;
+    const float m = 0.999f, c = 1e-3f;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = fmaf(v[k], m, c);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += v[k];
+    if (s == 123.456f) out[0] = s;
+  } else {
+    f32x2 v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = pack2(seed + k, seed - k);
+    const f32x2 m = pack2(0.999f, 0.998f), c = pack2(1e-3f, 2e-3f);
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = fma2(v[k], m, c);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { float lo, hi; unpack2(v[k], lo, hi); s += lo + hi; }
+    if (s == 123.456f) out[0] = s;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host-side dispatch
+// ---------------------------------------------------------------------------------------------
+template <typename T, int DIM>
+static int launch_nn(const NNArgs& a, const IcpPlan& pl, cudaStream_t st) {
+  dim3 grid(pl.qtiles, pl.S, pl.N);
+  nn_search_kernel<T, DIM><<<grid, NN_THREADS, 0, st>>>(a);
+  return check_launch();
+}
+
+template <typename T, int ICP, int DIM>
+static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* source, const void* target,
+                       const void* T_init, const void* weight, void* T_out, void* pc_out, void* deltas,
+                       void* weights_hist, void* costs, uint8_t* converged, void* iterations, void* matched_ratio,
+                       int32_t* iters_done, void* saved, void* workspace, cudaStream_t st) {
+  IcpWorkspace w = carve_workspace(workspace, pl);
+  IcpSaved sv = carve_saved(saved, pl, p->max_iterations);
+  const int save = (p->save_for_backward && saved) ? 1 : 0;
+  int rc;
+
+  init_state_kernel<T><<<(pl.N + 127) / 128, 128, 0, st>>>(static_cast<const T*>(T_init), w, pl.N);
+  if ((rc = check_launch())) return rc;
+  {
+    const size_t total = (size_t)pl.N * pl.mp;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    pack_targets_kernel<T><<<blocks, 256, 0, st>>>(static_cast<const T*>(target), p->target_cols, pl.N, pl.m, pl.mp,
+                                                    w.tx, w.ty, w.tz);
+    if ((rc = check_launch())) return rc;
+  }
+
+  NNArgs na;
+  na.source = source; na.target = target; na.pose = w.pose;
+  na.tx = w.tx; na.ty = w.ty; na.tz = w.tz;
+  na.frozen = w.frozen; na.counters = w.counters;
+  na.pd2 = w.pd2; na.pidx = w.pidx;
+  na.N = pl.N; na.n = pl.n; na.m = pl.m; na.mp = pl.mp; na.cols = p->target_cols;
+  na.tiles_per_slice = pl.tiles_per_slice; na.S = pl.S;
+
+  StepArgs sa;
+  sa.source = source; sa.target = target; sa.weight = p->has_weight ? weight : nullptr;
+  sa.w = w; sa.sv = sv;
+  sa.deltas = deltas; sa.weights_hist = weights_hist; sa.costs = costs;
+  sa.rp.differentiable = p->differentiable; sa.rp.use_trim = p->use_trim; sa.rp.loss_kind = p->loss_kind;
+  sa.rp.trim_dist = p->trim_dist; sa.rp.loss_metric = p->loss_metric; sa.rp.steep = p->tanh_steepness;
+  sa.N = pl.N; sa.n = pl.n; sa.m = pl.m; sa.cols = p->target_cols; sa.S = pl.S; sa.K = p->max_iterations;
+  sa.const_iter = p->const_iter; sa.save = save; sa.has_weight = p->has_weight && weight;
+  sa.tol = p->tolerance; sa.match_thresh = p->match_ratio_thresh;
+
+  for (int it = 0; it < p->max_iterations; ++it) {
+    na.idx_prev = it > 0 ? w.idx_cur : nullptr;
+    if ((rc = launch_nn<T, DIM>(na, pl, st))) return rc;
+    sa.it = it;
+    icp_step_kernel<T, ICP, DIM><<<pl.N, STEP_THREADS, 0, st>>>(sa);
+    if ((rc = check_launch())) return rc;
+  }
+  icp_finish_kernel<T, DIM><<<pl.N, 256, 0, st>>>(static_cast<const T*>(source), w, sv, save, pl.N, pl.n,
+                                                  static_cast<T*>(T_out), static_cast<T*>(pc_out), converged,
+                                                  static_cast<T*>(iterations), static_cast<T*>(matched_ratio),
+                                                  iters_done);
+  return check_launch();
+}
+
+template <typename T, int ICP, int DIM>
+static int run_backward(const mmb_icp_params* p, const IcpPlan& pl, const void* source, const void* target,
+                        const void* weight, const void* saved, const void* grad_T, const void* grad_pc,
+                        void* grad_source, void* grad_target, void* grad_T_init, void* grad_weight, cudaStream_t st) {
+  BwdArgs a;
+  a.source = source; a.target = target; a.weight = p->has_weight ? weight : nullptr;
+  a.sv = carve_saved(const_cast<void*>(saved), pl, p->max_iterations);
+  a.grad_T = grad_T; a.grad_pc = grad_pc;
+  a.grad_source = grad_source; a.grad_target = grad_target; a.grad_T_init = grad_T_init; a.grad_weight = grad_weight;
+  a.rp.differentiable = p->differentiable; a.rp.use_trim = p->use_trim; a.rp.loss_kind = p->loss_kind;
+  a.rp.trim_dist = p->trim_dist; a.rp.loss_metric = p->loss_metric; a.rp.steep = p->tanh_steepness;
+  a.N = pl.N; a.n = pl.n; a.m = pl.m; a.cols = p->target_cols; a.K = p->max_iterations;
+  a.has_weight = p->has_weight && weight;
+  icp_backward_kernel<T, ICP, DIM><<<pl.N, BWD_THREADS, 0, st>>>(a);
+  return check_launch();
+}
+
+static int validate(const mmb_icp_params* p) {
+  if (!p) return MMB_ERR_NULL_POINTER;
+  if (p->N <= 0 || p->n <= 0 || p->m <= 0 || p->max_iterations <= 0) return MMB_ERR_INVALID_SHAPE;
+  if (p->target_cols != 3 && p->target_cols != 6) return MMB_ERR_INVALID_SHAPE;
+  if (p->icp_type == MMB_PT2PL && p->target_cols != 6) return MMB_ERR_INVALID_SHAPE;
+  if (p->dtype != MMB_F32 && p->dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  if (p->icp_type != MMB_PT2PL && p->icp_type != MMB_PT2PT) return MMB_ERR_UNSUPPORTED;
+  if (p->dim != 2 && p->dim != 3) return MMB_ERR_UNSUPPORTED;
+  if (p->loss_kind < 0 || p->loss_kind > 2) return MMB_ERR_UNSUPPORTED;
+  return MMB_OK;
+}
+
+#define MMB_DISPATCH(p, FN, ...)                                                                       \
+  do {                                                                                                 \
+    const int key = (p->dtype == MMB_F64 ? 4 : 0) + (p->icp_type == MMB_PT2PT ? 2 : 0) + (p->dim == 3 ? 1 : 0); \
+    switch (key) {                                                                                     \
+      case 0: return FN<float, MMB_PT2PL, 2>(__VA_ARGS__);                                             \
+      case 1: return FN<float, MMB_PT2PL, 3>(__VA_ARGS__);                                             \
+      case 2: return FN<float, MMB_PT2PT, 2>(__VA_ARGS__);                                             \
+      case 3: return FN<float, MMB_PT2PT, 3>(__VA_ARGS__);                                             \
+      case 4: return FN<double, MMB_PT2PL, 2>(__VA_ARGS__);                                            \
+      case 5: return FN<double, MMB_PT2PL, 3>(__VA_ARGS__);                                            \
+      case 6: return FN<double, MMB_PT2PT, 2>(__VA_ARGS__);                                            \
+      default: return FN<double, MMB_PT2PT, 3>(__VA_ARGS__);                                           \
+    }                                                                                                  \
+  } while (0)
+
+}  // namespace mmb
+
+using namespace mmb;
+
+extern "C" {
+
+int mmb_abi_version(void) { return MMB_ABI_VERSION; }
+
+const char* mmb_status_string(int status) {
+  switch (status) {
+    case MMB_OK: return "ok";
+    case MMB_ERR_NULL_POINTER: return "null pointer";
+    case MMB_ERR_INVALID_SHAPE: return "invalid shape";
+    case MMB_ERR_UNSUPPORTED: return "unsupported dtype or option";
+    case MMB_ERR_WORKSPACE_TOO_SMALL: return "workspace too small";
+    case MMB_ERR_MISALIGNED: return "pointer not 16-byte aligned";
+    case MMB_ERR_CUDA: return "CUDA error";
+    default: return "unknown status";
+  }
+}
+
+const char* mmb_last_cuda_error(void) { return g_last_cuda_error; }
+
+size_t mmb_icp_workspace_bytes(const mmb_icp_params* p) {
+  if (validate(p)) return 0;
+  const IcpPlan pl = make_plan(p->N, p->n, p->m, p->icp_type, p->dim, p->nn_slices);
+  return carve_workspace(nullptr, pl).bytes;
+}
+
+size_t mmb_icp_saved_bytes(const mmb_icp_params* p) {
+  if (validate(p) || !p->save_for_backward) return 0;
+  const IcpPlan pl = make_plan(p->N, p->n, p->m, p->icp_type, p->dim, p->nn_slices);
+  return carve_saved(nullptr, pl, p->max_iterations).bytes;
+}
+
+int mmb_icp_forward(const mmb_icp_params* p, const void* source, const void* target, const void* T_init,
+                    const void* weight, void* T_out, void* pc_out, void* deltas, void* weights_hist, void* costs,
+                    uint8_t* converged, void* iterations, void* matched_ratio, int32_t* iters_done, void* saved,
+                    void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = validate(p);
+  if (rc) return rc;
+  if (!source || !target || !T_init || !T_out || !pc_out || !deltas || !weights_hist || !costs || !converged ||
+      !iterations || !matched_ratio || !iters_done || !workspace)
+    return MMB_ERR_NULL_POINTER;
+  if (p->has_weight && !weight) return MMB_ERR_NULL_POINTER;
+  if (p->save_for_backward && !saved) return MMB_ERR_NULL_POINTER;
+  if (reinterpret_cast<uintptr_t>(workspace) % 256) return MMB_ERR_MISALIGNED;
+  const IcpPlan pl = make_plan(p->N, p->n, p->m, p->icp_type, p->dim, p->nn_slices);
+  if (workspace_bytes < carve_workspace(nullptr, pl).bytes) return MMB_ERR_WORKSPACE_TOO_SMALL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  MMB_DISPATCH(p, run_forward, p, pl, source, target, T_init, weight, T_out, pc_out, deltas, weights_hist, costs,
+               converged, iterations, matched_ratio, iters_done, saved, workspace, st);
+}
+
+int mmb_icp_backward(const mmb_icp_params* p, const void* source, const void* target, const void* weight,
+                     const void* saved, const void* grad_T, const void* grad_pc, void* grad_source,
+                     void* grad_target, void* grad_T_init, void* grad_weight, void* workspace,
+                     size_t workspace_bytes, void* stream) {
+  (void)workspace; (void)workspace_bytes;
+  int rc = validate(p);
+  if (rc) return rc;
+  if (!source || !target || !saved) return MMB_ERR_NULL_POINTER;
+  const IcpPlan pl = make_plan(p->N, p->n, p->m, p->icp_type, p->dim, p->nn_slices);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  MMB_DISPATCH(p, run_backward, p, pl, source, target, weight, saved, grad_T, grad_pc, grad_source, grad_target,
+               grad_T_init, grad_weight, st);
+}
+
+size_t mmb_nn_workspace_bytes(int32_t N, int32_t n, int32_t m, int32_t nn_slices) {
+  if (N <= 0 || n <= 0 || m <= 0) return 0;
+  const IcpPlan pl = make_plan(N, n, m, MMB_PT2PL, 3, nn_slices);
+  return carve_workspace(nullptr, pl).bytes;
+}
+
+int mmb_nn_search(int32_t N, int32_t n, int32_t m, int32_t target_cols, int32_t dtype, int32_t dim,
+                  int32_t nn_slices, const void* query, const void* target, int32_t* idx_out, void* workspace,
+                  size_t workspace_bytes, void* stream) {
+  if (N <= 0 || n <= 0 || m <= 0 || (target_cols != 3 && target_cols != 6)) return MMB_ERR_INVALID_SHAPE;
+  if (dtype != MMB_F32 && dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  if (dim != 2 && dim != 3) return MMB_ERR_UNSUPPORTED;
+  if (!query || !target || !idx_out || !workspace) return MMB_ERR_NULL_POINTER;
+  if (reinterpret_cast<uintptr_t>(workspace) % 256) return MMB_ERR_MISALIGNED;
+  const IcpPlan pl = make_plan(N, n, m, MMB_PT2PL, 3, nn_slices);
+  IcpWorkspace w = carve_workspace(workspace, pl);
+  if (workspace_bytes < w.bytes) return MMB_ERR_WORKSPACE_TOO_SMALL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc;
+  identity_pose_kernel<<<(N + 127) / 128, 128, 0, st>>>(w.pose, N);
+  if ((rc = check_launch())) return rc;
+  const size_t total = (size_t)N * pl.mp;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (dtype == MMB_F32)
+    pack_targets_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(target), target_cols, N, m, pl.mp, w.tx, w.ty, w.tz);
+  else
+    pack_targets_kernel<double><<<blocks, 256, 0, st>>>(static_cast<const double*>(target), target_cols, N, m, pl.mp, w.tx, w.ty, w.tz);
+  if ((rc = check_launch())) return rc;
+  NNArgs na;
+  na.source = query; na.target = target; na.pose = w.pose;
+  na.tx = w.tx; na.ty = w.ty; na.tz = w.tz;
+  na.idx_prev = nullptr; na.frozen = nullptr; na.counters = nullptr;
+  na.pd2 = w.pd2; na.pidx = w.pidx;
+  na.N = N; na.n = n; na.m = m; na.mp = pl.mp; na.cols = target_cols;
+  na.tiles_per_slice = pl.tiles_per_slice; na.S = pl.S;
+  if (dtype == MMB_F32) rc = dim == 2 ? launch_nn<float, 2>(na, pl, st) : launch_nn<float, 3>(na, pl, st);
+  else rc = dim == 2 ? launch_nn<double, 2>(na, pl, st) : launch_nn<double, 3>(na, pl, st);
+  if (rc) return rc;
+  const size_t nq = (size_t)N * n;
+  merge_only_kernel<<<(int)((nq + 255) / 256), 256, 0, st>>>(w.pd2, w.pidx, pl.S, N, n, idx_out);
+  return check_launch();
+}
+
+int mmb_fp32_probe(int32_t blocks, int32_t iters, int32_t packed, float* out, void* stream) {
+  if (!out || blocks <= 0 || iters <= 0) return MMB_ERR_INVALID_SHAPE;
+  fp32_probe_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(iters, packed, out);
+  return check_launch();
+}
+
+}  // extern "C"

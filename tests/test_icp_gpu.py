@@ -1,0 +1,140 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the reference's golden vectors
+(tests/golden) and against the CPU oracle on the same seeded inputs."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import dicp_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+SYNTH = ["synth_pt2pl_dim2_cauchy", "synth_pt2pl_dim2_cauchy_hard", "synth_pt2pl_dim2_nondiff",
+         "synth_pt2pt_dim2_cauchy", "synth_pt2pl_dim3_huber", "synth_pt2pt_dim3_plain",
+         "synth_pt2pl_dim3_hardhuber"]
+FIXTURE = ["fixture_pt2pt_diff", "fixture_pt2pl_diff", "fixture_pt2pt_nondiff", "fixture_pt2pl_cauchy_nondiff"]
+
+
+def _icp(meta, tmp_path=None):
+    from mm_masking_b200.dICP import ICP
+    alg = ICP(icp_type=meta["icp_type"], differentiable=meta["differentiable"],
+              max_iterations=meta["max_iterations"], tolerance=meta["tolerance"])
+    alg.const_iter = meta["const_iter"]
+    return alg
+
+
+def _run(d, meta, dtype, grads=True, device="cuda"):
+    tt = lambda a: torch.tensor(np.asarray(a), dtype=dtype, device=device)
+    src = tt(d["in_source"]).requires_grad_(grads)
+    tgt = tt(d["in_target"] if meta["icp_type"] == "pt2pl" else d["in_target"][..., :3]).requires_grad_(grads)
+    T0 = tt(d["in_T_init"]).requires_grad_(grads)
+    w = tt(d["in_weight"]).requires_grad_(grads) if "in_weight" in d else None
+    out = _icp(meta).icp(src, tgt, T0, weight=w, trim_dist=meta["trim_dist"], loss_fn=meta["loss_fn"], dim=meta["dim"])
+    return out, (src, tgt, T0, w)
+
+
+def _pose_err(T, T_ref):
+    """max translation error (m) and rotation angle error (rad) over the batch."""
+    T = np.asarray(T, dtype=np.float64); T_ref = np.asarray(T_ref, dtype=np.float64)
+    dt = np.abs(T[:, :3, 3] - T_ref[:, :3, 3]).max()
+    dR = np.einsum("bij,bkj->bik", T[:, :3, :3], T_ref[:, :3, :3])
+    ang = np.arccos(np.clip((np.trace(dR, axis1=1, axis2=2) - 1) / 2, -1, 1))
+    # arccos loses precision near 0; use the skew part instead
+    sk = np.stack([dR[:, 2, 1] - dR[:, 1, 2], dR[:, 0, 2] - dR[:, 2, 0], dR[:, 1, 0] - dR[:, 0, 1]], 1) / 2
+    return dt, np.linalg.norm(sk, axis=1).max()
+
+
+@pytest.mark.parametrize("name", FIXTURE + SYNTH)
+def test_fp64_matches_reference(name, golden):
+    """Everything the reference returns, on fp64 inputs, against the reference's own fp64 run."""
+    d, meta = golden(name)
+    out, (src, tgt, T0, w) = _run(d, meta, torch.float64)
+    it = d["ref_deltas"].shape[1]
+    assert out["deltas"].shape == d["ref_deltas"].shape
+    assert out["weights"].shape == d["ref_weights"].shape and out["costs"].shape == d["ref_costs"].shape
+    np.testing.assert_allclose(out["T"].detach().cpu().numpy(), d["ref_T"], atol=1e-10, rtol=0)
+    np.testing.assert_allclose(out["pc"].detach().cpu().numpy(), d["ref_pc"], atol=1e-8, rtol=0)
+    np.testing.assert_allclose(out["deltas"].cpu().numpy(), d["ref_deltas"], atol=1e-10, rtol=0)
+    np.testing.assert_allclose(out["weights"].cpu().numpy(), d["ref_weights"], atol=1e-11, rtol=0)
+    np.testing.assert_allclose(out["costs"].cpu().numpy(), d["ref_costs"], atol=1e-9, rtol=1e-9)
+    assert np.array_equal(out["stats"]["converged"].cpu().numpy(), d["ref_converged"])
+    np.testing.assert_array_equal(out["stats"]["iterations"].cpu().numpy(), d["ref_iterations"])
+    np.testing.assert_allclose(out["stats"]["matched_ratio"].cpu().numpy(), d["ref_matched_ratio"], atol=1e-12)
+    G_T = torch.tensor(d["ref_G_T"], device="cuda"); G_pc = torch.tensor(d["ref_G_pc"], device="cuda")
+    ((out["T"] * G_T).sum() + (out["pc"] * G_pc).sum()).backward()
+    for key, t in (("source", src), ("target", tgt), ("T_init", T0), ("weight", w)):
+        if t is None:
+            continue
+        ref = d["ref_grad_" + key]
+        if np.isnan(ref).any():
+            assert not torch.isnan(t.grad).any()
+            continue
+        scale = max(np.abs(ref).max(), 1e-30)
+        assert np.abs(t.grad.cpu().numpy() - ref).max() <= 1e-7 * scale, key
+
+
+@pytest.mark.parametrize("name", SYNTH)
+def test_fp32_within_north_star_tolerances(name, golden):
+    """fp32 inputs (the training dtype): poses within 1e-5 m / 1e-6 rad and gradients within 1e-4
+    relative of the reference evaluated in fp64 on the same fp32-valued inputs."""
+    d, meta = golden(name)
+    out, (src, tgt, T0, w) = _run(d, meta, torch.float32)
+    dt, dr = _pose_err(out["T"].detach().cpu().numpy(), d["ref_T"])
+    assert dt < 1e-5 and dr < 1e-6, (dt, dr)
+    dt32, dr32 = _pose_err(d["ref_T_fp32_default_cdist"], d["ref_T"])
+    print(f"{name}: ours vs fp64 reference {dt:.2e} m / {dr:.2e} rad; reference's own fp32 run {dt32:.2e} m / {dr32:.2e} rad")
+    np.testing.assert_array_equal(out["stats"]["iterations"].cpu().numpy(), d["ref_iterations"])
+    G_T = torch.tensor(d["ref_G_T"], device="cuda", dtype=torch.float32)
+    G_pc = torch.tensor(d["ref_G_pc"], device="cuda", dtype=torch.float32)
+    ((out["T"] * G_T).sum() + (out["pc"] * G_pc).sum()).backward()
+    for key, t in (("source", src), ("target", tgt), ("T_init", T0), ("weight", w)):
+        ref = d["ref_grad_" + key]
+        if np.isnan(ref).any():
+            continue
+        scale = max(np.abs(ref).max(), 1e-30)
+        assert np.abs(t.grad.double().cpu().numpy() - ref).max() <= 1e-4 * scale, key
+
+
+def _replay_queries(d, meta, k):
+    """Source points in the target frame at the start of iteration k, from the golden deltas."""
+    src = torch.tensor(d["in_source"], dtype=torch.float64)
+    if meta["dim"] == 2:
+        src = src * torch.tensor([1.0, 1.0, 0.0], dtype=torch.float64)
+    T0 = torch.tensor(d["in_T_init"], dtype=torch.float64)
+    C, r = T0[:, :3, :3], T0[:, :3, 3]
+    deltas = torch.tensor(d["ref_deltas"], dtype=torch.float64)
+    for i in range(k):
+        C = O.so3_exp(deltas[:, i, 0:3, 0]).transpose(1, 2) @ C
+        r = r - deltas[:, i, 3:6, 0]
+    return src @ C.transpose(1, 2) + r[:, None, :]
+
+
+@pytest.mark.parametrize("name", FIXTURE[:2] + SYNTH)
+@pytest.mark.parametrize("slices", [0, 3])
+def test_correspondence_indices_bit_exact(name, slices, golden):
+    """Indices of every iteration equal the reference's (exact-difference cdist, fp64)."""
+    from mm_masking_b200.dICP.nn import nearest_index
+    d, meta = golden(name)
+    tgt = torch.tensor(d["in_target"], dtype=torch.float64, device="cuda")
+    if meta["dim"] == 2:
+        tgt = tgt * torch.tensor([1.0, 1.0, 0.0, 1.0, 1.0, 0.0], dtype=torch.float64, device="cuda")[: tgt.shape[2]]
+    ref_idx = d["ref_indices"]
+    for k in range(ref_idx.shape[0]):
+        q = _replay_queries(d, meta, k).cuda()
+        idx = nearest_index(q, tgt, dim=meta["dim"], nn_slices=slices).cpu().numpy()
+        mism = int((idx != ref_idx[k]).sum())
+        assert mism == 0, f"iteration {k}: {mism} of {idx.size} indices differ"
+
+
+def test_known_answer_pose(golden):
+    """`external/dICP/tests/test_ICP.py:35-148`: the fixture pose to 1e-10 and the aligned cloud."""
+    for name in FIXTURE[:3]:
+        d, meta = golden(name)
+        out, (src, tgt, T0, w) = _run(d, meta, torch.float64, device="cpu")     # CPU tensors, like the reference test
+        assert out["T"].device.type == "cpu"
+        T_true = torch.linalg.inv(O.se3_exp([1.0, 1.0, 0, 0, 0, 0.1]))
+        err = O.se3_log(T_true @ torch.linalg.inv(out["T"][0].detach()))
+        assert float(torch.linalg.norm(err)) < 1e-10
+        assert np.allclose(out["pc"][0].detach().numpy(), d["in_target"][0, :, :3], atol=1e-5)
+        out["T"].sum().backward()
+        assert src.grad is not None and tgt.grad is not None
+        assert not torch.isnan(src.grad).any() and not torch.isnan(tgt.grad).any()

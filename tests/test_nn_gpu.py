@@ -1,0 +1,81 @@
+"""GPU: nearest-neighbour search (K3) -- the reference's toy test, tie-breaking, and the oracle
+on random clouds, through `mmb_nn_search`."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import dicp_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def test_toy_points():
+    """`external/dICP/tests/test_nn.py:9-41`"""
+    from mm_masking_b200.dICP import nn
+    pts = torch.tensor([(5.0, 4.0, 0.0), (2.0, 6.0, 0.0), (13.0, 3.0, 0.0), (8.0, 7.0, 0.0), (3.0, 1.0, 0.0)],
+                       requires_grad=True)
+    q = torch.tensor([[9.0, 4.0, 0.0]], requires_grad=True)
+    finder = nn(differentiable=True, use_gumbel=False)
+    near = finder.find_nn(q, pts)
+    assert torch.all(near == torch.tensor((8.0, 7.0, 0.0)))
+    near.sum().backward()
+    assert pts.grad is not None and not torch.isnan(pts.grad).any()
+    pts2 = torch.cat((pts.detach(), torch.tensor([[10.0, 2.0, 0.0]])))
+    assert torch.all(finder.find_nn(q, pts2) == torch.tensor((10.0, 2.0, 0.0)))
+    nondiff = nn(differentiable=False)
+    assert torch.all(nondiff.find_nn(q, pts2) == torch.tensor((10.0, 2.0, 0.0)))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+@pytest.mark.parametrize("dim", [2, 3])
+def test_exact_ties_take_the_lowest_index(dtype, dim):
+    from mm_masking_b200.dICP.nn import nearest_index
+    g = torch.Generator().manual_seed(5)
+    N, n, m = 2, 700, 5000
+    tgt = (torch.rand((N, m, 3), generator=g, dtype=torch.float64) * 160 - 80).to(dtype)
+    if dim == 2:
+        tgt[:, :, 2] = 0
+    # every target row exists 4 times, at scattered positions
+    tgt[:, 1250:2500] = tgt[:, :1250]
+    tgt[:, 2500:3750] = tgt[:, :1250].flip(1)
+    tgt[:, 3750:] = tgt[:, :1250]
+    q = tgt[:, torch.randperm(m, generator=g)[:n]].clone()           # queries coincide with targets: distance 0
+    q[:, ::2] += 0.01
+    if dim == 2:
+        q[:, :, 2] = 0
+    for slices in (0, 2, 5):
+        idx = nearest_index(q.cuda(), tgt.cuda(), dim=dim, nn_slices=slices).cpu()
+        ref = O.nearest_index(q.double(), tgt.double(), "exact")
+        assert torch.equal(idx, ref)
+        assert int(idx.max()) < 1250                                   # always the first copy
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 1), (1, 65, 65), (3, 513, 1025), (2, 2000, 7000), (1, 100, 50000)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_random_clouds_match_oracle(shape, dtype):
+    from mm_masking_b200.dICP.nn import nearest_index
+    N, n, m = shape
+    g = torch.Generator().manual_seed(N * 1000 + n + m)
+    tgt = (torch.rand((N, m, 6), generator=g, dtype=torch.float64) * 160 - 80).to(dtype)
+    q = (torch.rand((N, n, 3), generator=g, dtype=torch.float64) * 160 - 80).to(dtype)
+    if m > 10:
+        tgt[:, -m // 10:, :] = 80000.0                                  # padding rows (ICP.py:446)
+    for dim in (2, 3):
+        idx = nearest_index(q.cuda(), tgt.cuda(), dim=dim).cpu()
+        qq, tt = q.double().clone(), tgt[:, :, :3].double().clone()
+        if dim == 2:
+            qq[:, :, 2] = 0; tt[:, :, 2] = 0
+        assert torch.equal(idx, O.nearest_index(qq, tt, "exact"))
+
+
+def test_clustered_near_ties_fp64_queries():
+    """Queries that are not fp32-representable, next to tight clusters of targets: the fp32 filter
+    must hand every candidate within its error band to the exact comparison."""
+    from mm_masking_b200.dICP.nn import nearest_index
+    g = torch.Generator().manual_seed(9)
+    N, n, m = 1, 512, 4096
+    centers = torch.rand((N, m // 8, 3), generator=g, dtype=torch.float64) * 150 - 75
+    tgt = centers.repeat_interleave(8, dim=1) + 1e-6 * torch.randn((N, m, 3), generator=g, dtype=torch.float64)
+    q = centers[:, :n] + 1e-3 * torch.randn((N, n, 3), generator=g, dtype=torch.float64)
+    idx = nearest_index(q.cuda(), tgt.cuda(), dim=3).cpu()
+    assert torch.equal(idx, O.nearest_index(q, tgt, "exact"))
