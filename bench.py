@@ -1,0 +1,358 @@
+#!/usr/bin/env python
+"""Headline benchmark: batched weighted point-to-plane ICP, forward + backward.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c3|c5|small]
+
+One "step" = one pass of the hot path over one batch of synthetic scan/map pairs: the call
+`ICP.icp(source, target, T_init, weight, trim_dist=5, loss_fn=cauchy(1), dim=2)` that
+`mm_masking/icp_weight_policy.py:281` makes, followed by `T.sum().backward()` so that the
+per-point weight gradients the UNet needs are produced.  Workload c3 (BASELINE.json
+configs[2]): 32 pairs per GPU, 2 000 radar points vs 50 000 lidar map points, 10 iterations
+(`const_iter: True` so every pair does all 10).
+
+  value  pairs/s with inputs resident in HBM (CUDA events per step, L2 flushed between steps)
+  e2e    pairs/s through the same public call with HOST (pinned) inputs: H2D of source, target,
+         T_init, weight and D2H of T and d(loss)/d(weight) inside the timed region
+  roofline       the nearest-neighbour kernel (nn_search_kernel): 8 flop per (source, target)
+                 pair per launch / its CUDA-event duration, against the FP32 FMA-pipe rate
+                 measured in the same run by mmb_fp32_probe (MEASURED_PEAKS.json has no
+                 CUDA-core FP32 figure)
+  cpu_baseline   the oracle port of the reference algorithm (torch CPU, `torch.cdist` +
+                 `argmin` exactly as `external/dICP/dICP/nn.py:32-38`) on the box's host cores
+
+Multi-GPU (torchrun): pairs are independent, so each rank runs its own 32 pairs and there is no
+data-path collective; value = all ranks' pairs / max-over-ranks time ("weak").
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: N per GPU, n, m, iterations, dim, three_d
+    "c3": dict(N=32, n=2000, m=50000, iters=10, dim=2, three_d=False,
+               desc="batched weighted pt2pl ICP, 32 pairs/GPU, 2000 radar pts vs 50000 lidar map pts, 10 it, fwd+bwd"),
+    "c5": dict(N=32, n=2000, m=200000, iters=20, dim=3, three_d=True,
+               desc="SE(3) pt2pl ICP, 32 pairs/GPU, 2000 pts vs 200000 map pts, 20 it, fwd+bwd"),
+    "small": dict(N=4, n=500, m=5000, iters=5, dim=2, three_d=False, desc="smoke-sized"),
+}
+METRIC = "icp_pairs_per_sec_fwd_bwd"
+UNIT = "pairs/s"
+FLOP_PER_PAIR = 8          # 3 sub, 3 mul, 2 add: the distance `torch.cdist` evaluates
+
+
+def make_batch(wl, seed):
+    from mm_masking_b200 import synth
+    return synth.make_icp_batch(N=wl["N"], n=wl["n"], m=wl["m"], seed=seed, three_d=wl["three_d"])
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self, t0, t1):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = [r for t, r in self.rows if t0 <= t <= t1 + 0.15] or [r for _, r in self.rows]
+        for r in rows:
+            f = [x.strip() for x in r.split(",")]
+            try:
+                sm.append(float(f[0])); mx = max(mx, float(f[1]))
+            except Exception:
+                continue
+            for name, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU reference arm / cpu_baseline (oracle port; the one place bench.py executes oracle/)
+# ---------------------------------------------------------------------------------------------
+def cpu_reference_step(batch, wl, pairs):
+    """fwd+bwd of the reference algorithm on `pairs` pairs, on the host cores.  Returns seconds."""
+    import torch
+    from oracle import dicp_oracle as O
+    t = lambda a: torch.tensor(a[:pairs])
+    w = t(batch["weight"]).requires_grad_(True)
+    t0 = time.perf_counter()
+    out = O.dicp(t(batch["source"]), t(batch["target"]), t(batch["T_init"]), w, icp_type="pt2pl",
+                 max_iterations=wl["iters"], tolerance=1e-5, differentiable=True, trim_dist=5.0,
+                 loss_fn={"name": "cauchy", "metric": 1.0}, dim=wl["dim"], const_iter=True, nn_mode="cdist")
+    out["T"].sum().backward()
+    return time.perf_counter() - t0
+
+
+def run_reference(args, wl, rank, world):
+    import torch
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    pairs = max(1, min(wl["N"], args.ref_pairs))
+    sub = dict(wl, N=pairs)
+    batch = make_batch(sub, seed=0)
+    for _ in range(min(args.warmup, 1)):
+        cpu_reference_step(batch, wl, 1)
+    secs = [cpu_reference_step(batch, wl, pairs) for _ in range(args.steps)]
+    total = sum(secs)
+    value = pairs * args.steps / total
+    sample = f"{pairs} pair(s) x {wl['iters']} it fwd+bwd per step, {args.steps} steps, fp32, torch.cdist+argmin NN"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload + ": " + wl["desc"], "pairs_per_step": pairs, "n": wl["n"], "m": wl["m"],
+                   "iterations": wl["iters"], "dim": wl["dim"]},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+def run_ours(args, wl, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from mm_masking_b200 import _capi
+    from mm_masking_b200.dICP import ICP
+    from mm_masking_b200.dICP.ICP import _IcpFunction  # noqa: F401  (same code path as ICP.icp)
+
+    _capi.require_cuda()
+    lib = _capi.load_library()
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    batch = make_batch(wl, seed=rank)
+    N, n, m, K = wl["N"], wl["n"], wl["m"], wl["iters"]
+    host = {k: torch.from_numpy(batch[k]).pin_memory() for k in ("source", "target", "T_init", "weight")}
+    d_src, d_tgt, d_T0 = (host[k].to(dev) for k in ("source", "target", "T_init"))
+    d_w = host["weight"].to(dev).requires_grad_(True)
+    out_T = torch.empty((N, 4, 4), dtype=torch.float32).pin_memory()
+    out_gw = torch.empty((N, n), dtype=torch.float32).pin_memory()
+
+    alg = ICP(icp_type="pt2pl", differentiable=True, max_iterations=K, tolerance=1e-5)
+    alg.const_iter = True
+    call = dict(trim_dist=5.0, loss_fn={"name": "cauchy", "metric": 1.0}, dim=wl["dim"])
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
+
+    def step_resident():
+        d_w.grad = None
+        out = alg.icp(d_src, d_tgt, d_T0, weight=d_w, **call)
+        out["T"].sum().backward()
+        return out
+
+    def step_e2e():
+        src = host["source"].to(dev, non_blocking=True)
+        tgt = host["target"].to(dev, non_blocking=True)
+        T0 = host["T_init"].to(dev, non_blocking=True)
+        w = host["weight"].to(dev, non_blocking=True).requires_grad_(True)
+        out = alg.icp(src, tgt, T0, weight=w, **call)
+        out["T"].sum().backward()
+        out_T.copy_(out["T"].detach(), non_blocking=True)
+        out_gw.copy_(w.grad, non_blocking=True)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        barrier()
+        t0 = time.time()
+        for a, b in ev:
+            flush.fill_(1)                      # evict the previous step's data from L2 (untimed)
+            a.record()
+            fn()
+            b.record()
+        barrier()
+        t1 = time.time()
+        ms = sum(a.elapsed_time(b) for a, b in ev)
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms / steps, t0, t1
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.3)
+    ms_res, t0, t1 = timed(step_resident, args.steps, args.warmup)
+    ms_e2e, _, t1 = timed(step_e2e, args.steps, max(1, args.warmup // 2))
+    clocks = None
+    if sampler:
+        sampler.stop()
+        clocks = sampler.summary(t0, t1)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel: per-class CUDA-event timing of the same forward -----
+    p = _capi.IcpParams()
+    p.N, p.n, p.m, p.target_cols = N, n, m, 6
+    p.dtype, p.icp_type, p.dim, p.max_iterations = _capi.F32, _capi.PT2PL, wl["dim"], K
+    p.differentiable, p.const_iter, p.use_trim, p.trim_dist = 1, 1, 1, 5.0
+    p.loss_kind, p.loss_metric, p.has_weight, p.save_for_backward = _capi.LOSS_CAUCHY, 1.0, 1, 1
+    p.tolerance, p.tanh_steepness, p.match_ratio_thresh = 1e-5, 5.0, 0.1
+    ws_bytes, sv_bytes = lib.mmb_icp_workspace_bytes(p), lib.mmb_icp_saved_bytes(p)
+    f32 = dict(dtype=torch.float32, device=dev)
+    bufs = dict(ws=torch.empty(ws_bytes, dtype=torch.uint8, device=dev), sv=torch.empty(sv_bytes, dtype=torch.uint8, device=dev),
+                T=torch.empty((N, 4, 4), **f32), pc=torch.empty((N, n, 3), **f32), de=torch.zeros((N, K, 6), **f32),
+                wh=torch.zeros((N, K, n), **f32), co=torch.zeros((N, K), **f32),
+                cv=torch.zeros(N, dtype=torch.uint8, device=dev), it=torch.zeros(N, **f32), mr=torch.zeros(N, **f32),
+                idn=torch.zeros(1, dtype=torch.int32, device=dev))
+    ms3, cnt3 = (C.c_float * 3)(), (C.c_int32 * 3)()
+    acc_ms, acc_n = [0.0, 0.0, 0.0], [0, 0, 0]
+    w_det = d_w.detach()
+    for rep in range(2 + min(args.steps, 5)):
+        flush.fill_(1)
+        rc = lib.mmb_icp_forward_profiled(p, _capi.ptr(d_src), _capi.ptr(d_tgt), _capi.ptr(d_T0), _capi.ptr(w_det),
+                                          _capi.ptr(bufs["T"]), _capi.ptr(bufs["pc"]), _capi.ptr(bufs["de"]),
+                                          _capi.ptr(bufs["wh"]), _capi.ptr(bufs["co"]), _capi.ptr(bufs["cv"]),
+                                          _capi.ptr(bufs["it"]), _capi.ptr(bufs["mr"]), _capi.ptr(bufs["idn"]),
+                                          _capi.ptr(bufs["sv"]), _capi.ptr(bufs["ws"]), ws_bytes, _capi.stream_ptr(),
+                                          ms3, cnt3)
+        _capi.check(rc, "mmb_icp_forward_profiled")
+        if rep >= 2:
+            for c in range(3):
+                acc_ms[c] += ms3[c]; acc_n[c] += cnt3[c]
+    nn_ms = acc_ms[0] / max(acc_n[0], 1)            # average duration of one NN launch
+    step_ms = acc_ms[1] / max(acc_n[1], 1)
+    reps = max(1, acc_n[0] // K)
+    fwd_ms = sum(acc_ms) / reps
+
+    # FP32 pipe rate measured here (no CUDA-core FP32 figure in MEASURED_PEAKS.json)
+    probe_out = torch.zeros(4, **f32)
+    peak = {}
+    for packed in (0, 1):
+        blocks, iters = 148 * 8, 1 << 15
+        best = 1e30
+        for _ in range(4):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            _capi.check(lib.mmb_fp32_probe(blocks, iters, packed, _capi.ptr(probe_out), _capi.stream_ptr()), "probe")
+            b.record(); torch.cuda.synchronize()
+            best = min(best, a.elapsed_time(b))
+        peak["ffma2" if packed else "ffma"] = blocks * 256 * iters * 8 * 2 * (2 if packed else 1) / (best * 1e-3) / 1e12
+    peak_tf = max(peak.values())
+    nn_flop = FLOP_PER_PAIR * N * n * m
+    achieved_tf = nn_flop / (nn_ms * 1e-3) / 1e12
+
+    peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    hbm_peak = json.load(open(peaks_file)).get("hbm_gbs") if os.path.exists(peaks_file) else None
+
+    # ---- CPU baseline on this box's host cores (bounded sample) -------------------------------
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        pairs = max(1, min(N, args.ref_pairs))
+        cpu_reference_step(batch, wl, 1)                     # warm-up (thread pool, allocator)
+        secs = cpu_reference_step(batch, wl, pairs)
+        cpu = {"value": pairs / secs, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{pairs} pair(s) of this workload x {K} it fwd+bwd, fp32, torch.cdist+argmin NN, {secs:.1f} s"}
+
+    launches_per_step = (2 + 2 * K + 1) + 1                  # init, pack, K x (nn, step), finish; backward
+    h2d = sum(host[k].numel() * 4 for k in host)
+    d2h = out_T.numel() * 4 + out_gw.numel() * 4
+    line = {
+        "metric": METRIC, "value": world * N / (ms_res * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_res, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload + ": " + wl["desc"], "pairs_per_gpu": N, "n": n, "m": m, "iterations": K,
+                   "dim": wl["dim"], "icp_type": "pt2pl", "loss": "cauchy(1.0)", "trim_dist": 5.0, "const_iter": True,
+                   "l2": "flushed between steps (256 MiB fill, untimed); per-step CUDA events",
+                   "parallelism": f"independent pairs, {world} rank(s), no data-path collective"},
+        "e2e": {"value": world * N / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches_per_step * args.steps * 2,
+        "roofline": {"kernel": "nn_search_kernel", "bound": "fp32", "achieved": achieved_tf, "peak": peak_tf,
+                     "unit": "TFLOP/s", "frac": achieved_tf / peak_tf, "traffic": None,
+                     "flop_per_launch": nn_flop, "ms_per_launch": nn_ms,
+                     "peak_source": "mmb_fp32_probe in this run (max of FFMA and FFMA2 chains); "
+                                    "MEASURED_PEAKS.json has no CUDA-core FP32 entry",
+                     "peak_detail": peak, "share_of_forward": acc_ms[0] / max(sum(acc_ms), 1e-9),
+                     "forward_ms": fwd_ms, "step_kernel_ms_per_launch": step_ms,
+                     "hbm_gbs_measured_peak": hbm_peak},
+        "cpu_baseline": cpu,
+        "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--ref-pairs", type=int, default=2, help="pairs per CPU-reference step (bounded sample)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, wl, rank, world)
+    else:
+        run_ours(args, wl, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -90,6 +90,20 @@ int mmb_icp_forward(const mmb_icp_params* p, const void* source, const void* tar
                     void* workspace, size_t workspace_bytes, void* stream);
 
 /*
+ * mmb_icp_forward plus per-kernel-class device timing, for bench.py's roofline figures.  CUDA
+ * events are recorded on `stream` around every launch; the call synchronises on the last one
+ * and writes to HOST memory: host_ms[0..2] = summed durations (ms) of the nearest-neighbour
+ * launches, the step (residual/normal-equation/solve) launches and the rest (init, target
+ * packing, result assembly); host_launches[0..2] = number of timed intervals in each class.
+ */
+int mmb_icp_forward_profiled(const mmb_icp_params* p, const void* source, const void* target,
+                             const void* T_init, const void* weight, void* T_out, void* pc_out,
+                             void* deltas, void* weights_hist, void* costs, uint8_t* converged,
+                             void* iterations, void* matched_ratio, int32_t* iters_done,
+                             void* saved, void* workspace, size_t workspace_bytes, void* stream,
+                             float* host_ms, int32_t* host_launches);
+
+/*
  * Backward of mmb_icp_forward: the hand-derived adjoint of the unrolled iterations (what
  * autograd computes for ICP.py:130-250; correspondence indices are constants).
  *   grad_T (N,4,4) or NULL, grad_pc (N,n,3) or NULL: incoming gradients.

@@ -38,7 +38,9 @@ SIGNATURES = {
     "mmb_last_cuda_error": (C.c_char_p, []),
     "mmb_icp_workspace_bytes": (C.c_size_t, [C.POINTER(IcpParams)]),
     "mmb_icp_saved_bytes": (C.c_size_t, [C.POINTER(IcpParams)]),
-    "mmb_icp_forward": (C.c_int, [C.POINTER(IcpParams)] + [_P] * 14 + [C.c_size_t, _P]),
+    "mmb_icp_forward": (C.c_int, [C.POINTER(IcpParams)] + [_P] * 15 + [C.c_size_t, _P]),
+    "mmb_icp_forward_profiled": (C.c_int, [C.POINTER(IcpParams)] + [_P] * 15 + [C.c_size_t, _P,
+                                                                                 C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
     "mmb_icp_backward": (C.c_int, [C.POINTER(IcpParams)] + [_P] * 11 + [C.c_size_t, _P]),
     "mmb_nn_workspace_bytes": (C.c_size_t, [C.c_int32] * 4),
     "mmb_nn_search": (C.c_int, [C.c_int32] * 7 + [_P] * 4 + [C.c_size_t, _P]),

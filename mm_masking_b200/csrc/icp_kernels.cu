@@ -14,6 +14,8 @@
 //     host enqueues max_iterations rounds without synchronising.
 #include "mmb_common.cuh"
 
+#include <vector>
+
 namespace mmb {
 
 static thread_local char g_last_cuda_error[256] = "";
@@ -913,11 +915,25 @@ static int launch_nn(const NNArgs& a, const IcpPlan& pl, cudaStream_t st) {
   return check_launch();
 }
 
+// Optional per-kernel timing of one forward call (mmb_icp_forward_profiled): CUDA events are
+// recorded on the launch stream between the kernel classes; the normal path records nothing.
+struct ForwardProfile {
+  std::vector<cudaEvent_t> ev;     // boundaries
+  std::vector<int> cls;            // class of the interval that ENDS at ev[i+1]: 0 nn, 1 step, 2 other
+  cudaStream_t st;
+  void mark(int c) {
+    cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st);
+    if (!ev.empty()) cls.push_back(c);
+    ev.push_back(e);
+  }
+};
+
 template <typename T, int ICP, int DIM>
 static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* source, const void* target,
                        const void* T_init, const void* weight, void* T_out, void* pc_out, void* deltas,
                        void* weights_hist, void* costs, uint8_t* converged, void* iterations, void* matched_ratio,
-                       int32_t* iters_done, void* saved, void* workspace, cudaStream_t st) {
+                       int32_t* iters_done, void* saved, void* workspace, cudaStream_t st, ForwardProfile* prof) {
+  if (prof) { prof->st = st; prof->mark(2); }
   IcpWorkspace w = carve_workspace(workspace, pl);
   IcpSaved sv = carve_saved(saved, pl, p->max_iterations);
   const int save = (p->save_for_backward && saved) ? 1 : 0;
@@ -954,16 +970,21 @@ static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* s
 
   for (int it = 0; it < p->max_iterations; ++it) {
     na.idx_prev = it > 0 ? w.idx_cur : nullptr;
+    if (prof && it == 0) prof->mark(2);
     if ((rc = launch_nn<T, DIM>(na, pl, st))) return rc;
+    if (prof) prof->mark(0);
     sa.it = it;
     icp_step_kernel<T, ICP, DIM><<<pl.N, STEP_THREADS, 0, st>>>(sa);
     if ((rc = check_launch())) return rc;
+    if (prof) prof->mark(1);
   }
   icp_finish_kernel<T, DIM><<<pl.N, 256, 0, st>>>(static_cast<const T*>(source), w, sv, save, pl.N, pl.n,
                                                   static_cast<T*>(T_out), static_cast<T*>(pc_out), converged,
                                                   static_cast<T*>(iterations), static_cast<T*>(matched_ratio),
                                                   iters_done);
-  return check_launch();
+  rc = check_launch();
+  if (prof) prof->mark(2);
+  return rc;
 }
 
 template <typename T, int ICP, int DIM>
@@ -1045,10 +1066,11 @@ size_t mmb_icp_saved_bytes(const mmb_icp_params* p) {
   return carve_saved(nullptr, pl, p->max_iterations).bytes;
 }
 
-int mmb_icp_forward(const mmb_icp_params* p, const void* source, const void* target, const void* T_init,
-                    const void* weight, void* T_out, void* pc_out, void* deltas, void* weights_hist, void* costs,
-                    uint8_t* converged, void* iterations, void* matched_ratio, int32_t* iters_done, void* saved,
-                    void* workspace, size_t workspace_bytes, void* stream) {
+static int icp_forward_impl(const mmb_icp_params* p, const void* source, const void* target, const void* T_init,
+                            const void* weight, void* T_out, void* pc_out, void* deltas, void* weights_hist,
+                            void* costs, uint8_t* converged, void* iterations, void* matched_ratio,
+                            int32_t* iters_done, void* saved, void* workspace, size_t workspace_bytes, void* stream,
+                            ForwardProfile* prof) {
   int rc = validate(p);
   if (rc) return rc;
   if (!source || !target || !T_init || !T_out || !pc_out || !deltas || !weights_hist || !costs || !converged ||
@@ -1061,7 +1083,38 @@ int mmb_icp_forward(const mmb_icp_params* p, const void* source, const void* tar
   if (workspace_bytes < carve_workspace(nullptr, pl).bytes) return MMB_ERR_WORKSPACE_TOO_SMALL;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   MMB_DISPATCH(p, run_forward, p, pl, source, target, T_init, weight, T_out, pc_out, deltas, weights_hist, costs,
-               converged, iterations, matched_ratio, iters_done, saved, workspace, st);
+               converged, iterations, matched_ratio, iters_done, saved, workspace, st, prof);
+}
+
+int mmb_icp_forward(const mmb_icp_params* p, const void* source, const void* target, const void* T_init,
+                    const void* weight, void* T_out, void* pc_out, void* deltas, void* weights_hist, void* costs,
+                    uint8_t* converged, void* iterations, void* matched_ratio, int32_t* iters_done, void* saved,
+                    void* workspace, size_t workspace_bytes, void* stream) {
+  return icp_forward_impl(p, source, target, T_init, weight, T_out, pc_out, deltas, weights_hist, costs, converged,
+                          iterations, matched_ratio, iters_done, saved, workspace, workspace_bytes, stream, nullptr);
+}
+
+int mmb_icp_forward_profiled(const mmb_icp_params* p, const void* source, const void* target, const void* T_init,
+                             const void* weight, void* T_out, void* pc_out, void* deltas, void* weights_hist,
+                             void* costs, uint8_t* converged, void* iterations, void* matched_ratio,
+                             int32_t* iters_done, void* saved, void* workspace, size_t workspace_bytes, void* stream,
+                             float* host_ms, int32_t* host_launches) {
+  if (!host_ms || !host_launches) return MMB_ERR_NULL_POINTER;
+  ForwardProfile prof;
+  int rc = icp_forward_impl(p, source, target, T_init, weight, T_out, pc_out, deltas, weights_hist, costs, converged,
+                            iterations, matched_ratio, iters_done, saved, workspace, workspace_bytes, stream, &prof);
+  for (int c = 0; c < 3; ++c) { host_ms[c] = 0.f; host_launches[c] = 0; }
+  if (!prof.ev.empty()) {
+    if (cudaEventSynchronize(prof.ev.back()) != cudaSuccess && rc == MMB_OK) rc = MMB_ERR_CUDA;
+    for (size_t i = 0; i + 1 < prof.ev.size(); ++i) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, prof.ev[i], prof.ev[i + 1]) == cudaSuccess) {
+        host_ms[prof.cls[i]] += ms; host_launches[prof.cls[i]] += 1;
+      }
+    }
+    for (cudaEvent_t e : prof.ev) cudaEventDestroy(e);
+  }
+  return rc;
 }
 
 int mmb_icp_backward(const mmb_icp_params* p, const void* source, const void* target, const void* weight,
