@@ -70,7 +70,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except Exception:
@@ -253,8 +253,8 @@ def run_ours(args, wl, rank, world, local_rank):
                 wh=torch.zeros((N, K, n), **f32), co=torch.zeros((N, K), **f32),
                 cv=torch.zeros(N, dtype=torch.uint8, device=dev), it=torch.zeros(N, **f32), mr=torch.zeros(N, **f32),
                 idn=torch.zeros(1, dtype=torch.int32, device=dev))
-    ms3, cnt3 = (C.c_float * 3)(), (C.c_int32 * 3)()
-    acc_ms, acc_n = [0.0, 0.0, 0.0], [0, 0, 0]
+    ms3, cnt3 = (C.c_float * 4)(), (C.c_int32 * 4)()
+    acc_ms, acc_n = [0.0] * 4, [0] * 4
     w_det = d_w.detach()
     for rep in range(2 + min(args.steps, 5)):
         flush.fill_(1)
@@ -266,7 +266,7 @@ def run_ours(args, wl, rank, world, local_rank):
                                           ms3, cnt3)
         _capi.check(rc, "mmb_icp_forward_profiled")
         if rep >= 2:
-            for c in range(3):
+            for c in range(4):
                 acc_ms[c] += ms3[c]; acc_n[c] += cnt3[c]
     nn_ms = acc_ms[0] / max(acc_n[0], 1)            # average duration of one NN launch
     step_ms = acc_ms[1] / max(acc_n[1], 1)
@@ -304,7 +304,7 @@ def run_ours(args, wl, rank, world, local_rank):
         cpu = {"value": pairs / secs, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"{pairs} pair(s) of this workload x {K} it fwd+bwd, fp32, torch.cdist+argmin NN, {secs:.1f} s"}
 
-    launches_per_step = (2 + 2 * K + 1) + 1                  # init, pack, K x (nn, step), finish; backward
+    launches_per_step = (2 + 2 + 2 * K + 1) + 1              # init, pack, sub-pack, bound pass, K x (nn, step), finish; backward
     h2d = sum(host[k].numel() * 4 for k in host)
     d2h = out_T.numel() * 4 + out_gw.numel() * 4
     line = {
@@ -325,6 +325,7 @@ def run_ours(args, wl, rank, world, local_rank):
                                     "MEASURED_PEAKS.json has no CUDA-core FP32 entry",
                      "peak_detail": peak, "share_of_forward": acc_ms[0] / max(sum(acc_ms), 1e-9),
                      "forward_ms": fwd_ms, "step_kernel_ms_per_launch": step_ms,
+                     "bound_pass_ms": acc_ms[3] / reps,
                      "hbm_gbs_measured_peak": hbm_peak},
         "cpu_baseline": cpu,
         "clocks": clocks,

@@ -92,9 +92,10 @@ int mmb_icp_forward(const mmb_icp_params* p, const void* source, const void* tar
 /*
  * mmb_icp_forward plus per-kernel-class device timing, for bench.py's roofline figures.  CUDA
  * events are recorded on `stream` around every launch; the call synchronises on the last one
- * and writes to HOST memory: host_ms[0..2] = summed durations (ms) of the nearest-neighbour
- * launches, the step (residual/normal-equation/solve) launches and the rest (init, target
- * packing, result assembly); host_launches[0..2] = number of timed intervals in each class.
+ * and writes to HOST memory: host_ms[0..3] = summed durations (ms) of the nearest-neighbour
+ * launches, the step (residual/normal-equation/solve) launches, the rest (init, target
+ * packing, result assembly) and the cold-start bound pass (subsample pack + search);
+ * host_launches[0..3] = number of timed intervals in each class.
  */
 int mmb_icp_forward_profiled(const mmb_icp_params* p, const void* source, const void* target,
                              const void* T_init, const void* weight, void* T_out, void* pc_out,

@@ -34,10 +34,14 @@ constexpr int STEP_THREADS = 512;
 constexpr int BWD_THREADS = 512;
 constexpr float PAD_COORD = __builtin_huge_valf();   // filter copy padding: never passes the filter
 
+constexpr int NN_SUB_STRIDE = 8;       // cold start: bound pass over every 8th target (DESIGN.md "cold start")
+constexpr int NN_SUB_MIN_M = 8192;     // below this the bound pass is not worth a launch
+
 struct IcpPlan {
   int N, n, m, mp, R;            // mp: m rounded up to NN_TILE; R residual rows
   int qtiles, S, tiles_per_slice;
   int D;                         // solved DoF
+  int sub_stride, msub, msp, S_sub, sub_tiles_per_slice;   // strided subsample (0 = no bound pass)
 };
 
 static int pick_slices(int N, int qtiles, int tiles, int requested) {
@@ -74,6 +78,16 @@ static IcpPlan make_plan(int N, int n, int m, int icp_type, int dim, int nn_slic
   pl.tiles_per_slice = (tiles + pl.S - 1) / pl.S;
   pl.S = (tiles + pl.tiles_per_slice - 1) / pl.tiles_per_slice;
   pl.D = dim == 2 ? 3 : 6;
+  pl.sub_stride = 0; pl.msub = 0; pl.msp = 0; pl.S_sub = 0; pl.sub_tiles_per_slice = 0;
+  if (m >= NN_SUB_MIN_M) {
+    pl.sub_stride = NN_SUB_STRIDE;
+    pl.msub = (m + NN_SUB_STRIDE - 1) / NN_SUB_STRIDE;
+    pl.msp = (int)align_up((size_t)pl.msub, NN_TILE);
+    const int st = pl.msp / NN_TILE;
+    pl.S_sub = st < 8 ? st : 8;
+    pl.sub_tiles_per_slice = (st + pl.S_sub - 1) / pl.S_sub;
+    pl.S_sub = (st + pl.sub_tiles_per_slice - 1) / pl.sub_tiles_per_slice;
+  }
   return pl;
 }
 
@@ -81,7 +95,9 @@ static IcpPlan make_plan(int N, int n, int m, int icp_type, int dim, int nn_slic
 // Workspace / saved-state layouts
 // ---------------------------------------------------------------------------------------------
 struct IcpWorkspace {
-  float *tx, *ty, *tz;           // (N, mp) fp32 filter copy of the targets, SoA
+  float *tx, *ty, *tz, *tn;      // (N, mp) fp32 filter copy of the targets, SoA, and the deflated |t|^2
+  float *sx, *sy, *sz, *sn;      // (N, msp) the same for every NN_SUB_STRIDE-th target
+  float* bound;                  // (S_sub,N,n) min filter value over the subsample, per slice
   double* pose;                  // (N,12) current C (row-major) and r
   double* pd2; int* pidx;        // (S,N,n) per-slice partial minima
   int* idx_cur;                  // (N,n) correspondences of the latest search
@@ -100,7 +116,10 @@ static IcpWorkspace carve_workspace(void* base, const IcpPlan& pl) {
   Carver c(base);
   IcpWorkspace w;
   const size_t Nmp = (size_t)pl.N * pl.mp, Nn = (size_t)pl.N * pl.n;
-  w.tx = c.take<float>(Nmp); w.ty = c.take<float>(Nmp); w.tz = c.take<float>(Nmp);
+  w.tx = c.take<float>(Nmp); w.ty = c.take<float>(Nmp); w.tz = c.take<float>(Nmp); w.tn = c.take<float>(Nmp);
+  const size_t Nms = (size_t)pl.N * pl.msp;
+  w.sx = c.take<float>(Nms); w.sy = c.take<float>(Nms); w.sz = c.take<float>(Nms); w.sn = c.take<float>(Nms);
+  w.bound = c.take<float>((size_t)pl.S_sub * Nn);
   w.pose = c.take<double>((size_t)pl.N * 12);
   w.pd2 = c.take<double>((size_t)pl.S * Nn);
   w.pidx = c.take<int>((size_t)pl.S * Nn);
@@ -169,37 +188,63 @@ __global__ void identity_pose_kernel(double* pose, int N) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// pack: AoS targets of either dtype -> fp32 SoA filter copy, padded to the tile size with +inf
+// pack: AoS targets of either dtype -> fp32 SoA filter copy (x, y, z, n) padded to the tile size.
+// n = |t~|^2 (1 - 2^-19) rounded down, t~ the fp32-rounded coordinates (z left out when dim == 2);
+// pad rows get x = y = z = 0 and n = +inf so they never pass the filter.
 // ---------------------------------------------------------------------------------------------
+constexpr double FILTER_MARGIN = 1.9073486328125e-06;       // 2^-19 = 32 * 2^-24, see DESIGN.md "NN filter"
+
+// Packed element j of pair b is target row j * stride (stride 1: the full copy; NN_SUB_STRIDE: the
+// subsample of the bound pass); mc = number of packed rows that exist, mp = padded length.
 template <typename T>
-__global__ void pack_targets_kernel(const T* __restrict__ target, int cols, int N, int m, int mp, float* __restrict__ tx,
-                                    float* __restrict__ ty, float* __restrict__ tz) {
+__global__ void pack_targets_kernel(const T* __restrict__ target, int cols, int N, int m, int mc, int mp, int stride,
+                                    int dim, float* __restrict__ tx, float* __restrict__ ty, float* __restrict__ tz,
+                                    float* __restrict__ tn) {
   const size_t total = (size_t)N * mp;
   for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (size_t)gridDim.x * blockDim.x) {
     const int b = (int)(g / mp), j = (int)(g % mp);
-    float x = PAD_COORD, y = PAD_COORD, z = PAD_COORD;
-    if (j < m) {
-      const T* row = target + ((size_t)b * m + j) * cols;
-      x = (float)row[0]; y = (float)row[1]; z = (float)row[2];
+    float x = 0.f, y = 0.f, z = 0.f, nn = PAD_COORD;
+    if (j < mc) {
+      const T* row = target + ((size_t)b * m + (size_t)j * stride) * cols;
+      x = (float)row[0]; y = (float)row[1]; z = dim == 3 ? (float)row[2] : 0.f;
+      const double n2 = (double)x * x + (double)y * y + (double)z * z;
+      nn = __double2float_rd(n2 * (1.0 - FILTER_MARGIN));
     }
-    tx[g] = x; ty[g] = y; tz[g] = z;
+    tx[g] = x; ty[g] = y; tz[g] = z; tn[g] = nn;
   }
 }
 
 // ---------------------------------------------------------------------------------------------
 // K3: nearest neighbour
 // ---------------------------------------------------------------------------------------------
-// Filter threshold on the fp32 squared distance for an exact best squared distance D2 (fp64).
-// Derivation (DESIGN.md "NN filter"): with u = 2^-24, every fp32-evaluated d~^2 of a candidate
-// whose true distance d <= D satisfies d~^2 <= (D(1+3u) + 3u|q|_1)^2 (1+8u); we use 2^-22
-// for u (4x margin) and round up.
-__device__ __forceinline__ float filter_threshold(double D2, double qnorm1) {
+// The streaming loop evaluates, for query q and target t, the expansion
+//     F = n_t - 2 q~.t~           (n_t the deflated |t~|^2 of the pack kernel; fp32 FFMA2 chain)
+// which differs from d^2 - |q~|^2 only by rounding.  With u = 2^-24 and the fp32-rounded copies
+// t~, q~ of the exact fp64 points (DESIGN.md "NN filter" has the derivation):
+//     F <= d^2 - |q~|^2 - 21u |t~|^2 + 11u |q~|^2          for every target,
+// so every target with d^2 <= D2 (ties included) satisfies F <= D2 - |q~|^2 + 32u |q~|^2 =: thr.
+// Targets that pass are compared exactly in fp64 on the caller's own coordinates.
+__device__ __forceinline__ float filter_threshold(double D2, float fqx, float fqy, float fqz) {
   if (!(D2 < 1.0e300)) return FLT_MAX;
-  const double u = 2.384185791015625e-07;      // 2^-22
-  const double Tb = sqrt(D2) * (1.0 + 3.0 * u) + 3.0 * u * qnorm1;
-  const double t2 = Tb * Tb * (1.0 + 8.0 * u);
-  if (t2 >= 3.0e38) return FLT_MAX;
-  return __double2float_ru(t2);
+  const double qn = (double)fqx * fqx + (double)fqy * fqy + (double)fqz * fqz;
+  const double t = D2 - qn + qn * FILTER_MARGIN;
+  if (t >= 3.0e38) return FLT_MAX;
+  if (t <= -3.0e38) return -FLT_MAX;
+  return __double2float_ru(t);
+}
+
+// Threshold from the smallest filter value f seen over ANY subset of the targets.  With the
+// two-sided version of the bound above, F >= d^2 - |q~|^2 - 45u |t~|^2 - 11u |q~|^2, and
+// |t| <= |q| + d for the target that attains f, the true nearest distance obeys
+//     D*^2 <= d^2 <= (f + |q~|^2 + 101u |q~|^2) / (1 - 90u) =: B,
+// and filter_threshold(B) lets every target with d^2 <= B through.
+__device__ __forceinline__ float bound_threshold(float f, float fqx, float fqy, float fqz) {
+  if (!(f < 3.0e38f)) return FLT_MAX;
+  const double u = 5.9604644775390625e-08;      // 2^-24
+  const double qn = (double)fqx * fqx + (double)fqy * fqy + (double)fqz * fqz;
+  double B = ((double)f + qn + 101.0 * u * qn) / (1.0 - 90.0 * u);
+  if (!(B > 0.0)) B = 0.0;
+  return filter_threshold(B, fqx, fqy, fqz);
 }
 
 template <typename T, int DIM>
@@ -213,24 +258,44 @@ __device__ __forceinline__ double exact_dist2(const T* __restrict__ row, double 
   return d2;
 }
 
+// The query in the target frame, fp64, with the operation order every kernel shares.
+template <typename T, int DIM>
+__device__ __forceinline__ void transform_query(const T* __restrict__ src_row, const double* __restrict__ P, double& qx,
+                                                double& qy, double& qz) {
+  const double px = (double)src_row[0], py = (double)src_row[1];
+  const double pz = DIM == 3 ? (double)src_row[2] : 0.0;
+  double ax, ay, az;
+  rotate_point(P, px, py, pz, ax, ay, az);
+  qx = __dadd_rn(ax, P[9]); qy = __dadd_rn(ay, P[10]); qz = __dadd_rn(az, P[11]);
+}
+
 struct ExactState { double D2; int I; float thr; };
 
-// Cold path of the search: candidates whose fp32 distance passed the filter are compared exactly
-// (fp64 on the caller's own coordinates), lowest index winning ties.  Kept out of line so the
-// streaming loop stays compact in the instruction cache.
+constexpr int NN_G = 8;           // targets per filter group (one branch per NN_R x NN_G pairs)
+
+// Cold path of the search: in a group of NN_G targets at least one passed the filter.  Each is
+// re-filtered on its own (the scalar FFMA chain below produces the same bits as the packed one of
+// the streaming loop) and the survivors are compared exactly (fp64 on the caller's own
+// coordinates), lowest index winning ties.  Kept out of line so the streaming loop stays compact
+// in the instruction cache.
 template <typename T, int DIM>
-__device__ __noinline__ ExactState exact_path(const T* __restrict__ tgt, int cols, int m, int j0, float d0, float d1,
-                                              float d2, float d3, float thr, double qx, double qy, double qz,
-                                              double qn1, double D2, int I) {
-  const float dd[4] = {d0, d1, d2, d3};
-#pragma unroll
-  for (int c = 0; c < 4; ++c) {
+__device__ __noinline__ ExactState exact_group(const T* __restrict__ tgt, int cols, int m, int j0,
+                                               const T* __restrict__ src_row, const double* __restrict__ P,
+                                               const float* __restrict__ gx, const float* __restrict__ gy,
+                                               const float* __restrict__ gz, const float* __restrict__ gn, float fx,
+                                               float fy, float fz, double D2, int I, float thr) {
+  double qx, qy, qz;
+  transform_query<T, DIM>(src_row, P, qx, qy, qz);
+#pragma unroll 1
+  for (int c = 0; c < NN_G; ++c) {
+    float f = fmaf(gy[c], fy, fmaf(gx[c], fx, gn[c]));
+    if (DIM == 3) f = fmaf(gz[c], fz, f);
     const int j = j0 + c;
-    if (dd[c] <= thr && j < m) {
+    if (f <= thr && j < m) {
       const double e2 = exact_dist2<T, DIM>(tgt + (size_t)j * cols, qx, qy, qz);
       if (e2 < D2 || (e2 == D2 && j < I)) {
         D2 = e2; I = j;
-        thr = filter_threshold(e2, qn1);
+        thr = filter_threshold(D2, (float)qx, (float)qy, DIM == 3 ? (float)qz : 0.f);
       }
     }
   }
@@ -242,15 +307,20 @@ struct NNArgs {
   const void* source;        // (N,n,3) points that are rotated/translated by pose before the search
   const void* target;        // (N,m,cols) exact targets
   const double* pose;        // (N,12)
-  const float *tx, *ty, *tz; // filter copy
+  const float *tx, *ty, *tz, *tn; // filter copy
   const int* idx_prev;       // (N,n) warm start or nullptr
+  const float* bound_in;     // (bound_S,N,n) cold start: min filter value over a subsample, or nullptr
+  float* bound_out;          // bound pass: (S,N,n) min filter value of this slice
+  int bound_S;
   const int* frozen;         // (N) or nullptr
   const int* counters;       // done flag at [1], or nullptr
   double* pd2; int* pidx;    // (S,N,n)
   int N, n, m, mp, cols, tiles_per_slice, S;
 };
 
-template <typename T, int DIM>
+// BOUND = false: the search proper.  BOUND = true: the cold-start bound pass -- the same streaming
+// loop over the strided subsample with no exact path; it only records the smallest filter value.
+template <typename T, int DIM, bool BOUND>
 __global__ void __launch_bounds__(NN_THREADS) nn_search_kernel(NNArgs a) {
   const int qt = blockIdx.x, s = blockIdx.y, b = blockIdx.z;
   if (a.counters && a.counters[1]) return;
@@ -259,6 +329,7 @@ __global__ void __launch_bounds__(NN_THREADS) nn_search_kernel(NNArgs a) {
   __shared__ __align__(128) float sx[2][NN_TILE];
   __shared__ __align__(128) float sy[2][NN_TILE];
   __shared__ __align__(128) float sz[2][DIM == 3 ? NN_TILE : 4];
+  __shared__ __align__(128) float sn[2][NN_TILE];
   __shared__ __align__(8) uint64_t bar[2];
   __shared__ double sC[12];
 
@@ -276,38 +347,45 @@ __global__ void __launch_bounds__(NN_THREADS) nn_search_kernel(NNArgs a) {
   auto issue = [&](int k) {
     const int buf = k & 1;
     const size_t off = tbase + (size_t)(tile0 + k) * NN_TILE;
-    mbar_expect_tx(&bar[buf], kTileBytes * DIM);
+    mbar_expect_tx(&bar[buf], kTileBytes * (DIM + 1));
     bulk_g2s(sx[buf], a.tx + off, kTileBytes, &bar[buf]);
     bulk_g2s(sy[buf], a.ty + off, kTileBytes, &bar[buf]);
     if (DIM == 3) bulk_g2s(sz[buf], a.tz + off, kTileBytes, &bar[buf]);
+    bulk_g2s(sn[buf], a.tn + off, kTileBytes, &bar[buf]);
   };
   if (tid == 0 && ntiles > 0) issue(0);
 
-  // ---- per-thread queries -------------------------------------------------------------------
+  // ---- per-thread queries: hot state is (-2q~, thr) in fp32; (D2, I) persist for the exact path -----
   const T* src = static_cast<const T*>(a.source) + (size_t)b * a.n * 3;
   const T* tgt = static_cast<const T*>(a.target) + (size_t)b * a.m * a.cols;
-  double qx[NN_R], qy[NN_R], qz[NN_R], qn1[NN_R], D2[NN_R];
+  double D2[NN_R];
   float fx[NN_R], fy[NN_R], fz[NN_R], thr[NN_R];
   int I[NN_R];
 #pragma unroll
   for (int r = 0; r < NN_R; ++r) {
     const int qi = qt * NN_QB + r * NN_THREADS + tid;
-    qx[r] = qy[r] = qz[r] = 0.0; qn1[r] = 0.0; D2[r] = 1.0e308; I[r] = INT_MAX;
-    thr[r] = -1.0f;                      // lanes past n never reach the exact path
+    D2[r] = 1.0e308; I[r] = INT_MAX;
+    fx[r] = fy[r] = fz[r] = 0.f;
+    thr[r] = -FLT_MAX;                   // lanes past n never reach the exact path
     if (qi < a.n) {
-      const double px = (double)src[(size_t)qi * 3 + 0], py = (double)src[(size_t)qi * 3 + 1];
-      const double pz = DIM == 3 ? (double)src[(size_t)qi * 3 + 2] : 0.0;
-      double ax, ay, az;
-      rotate_point(sC, px, py, pz, ax, ay, az);
-      qx[r] = __dadd_rn(ax, sC[9]); qy[r] = __dadd_rn(ay, sC[10]); qz[r] = __dadd_rn(az, sC[11]);
-      qn1[r] = fabs(qx[r]) + fabs(qy[r]) + (DIM == 3 ? fabs(qz[r]) : 0.0);
-      if (a.idx_prev) {
-        int j0 = a.idx_prev[(size_t)b * a.n + qi];
-        if (j0 >= 0 && j0 < a.m) D2[r] = exact_dist2<T, DIM>(tgt + (size_t)j0 * a.cols, qx[r], qy[r], qz[r]);
+      double qx, qy, qz;
+      transform_query<T, DIM>(src + (size_t)qi * 3, sC, qx, qy, qz);
+      const float gx = (float)qx, gy = (float)qy, gz = DIM == 3 ? (float)qz : 0.f;
+      if (BOUND) {
+        thr[r] = FLT_MAX;                // running minimum of the filter value
+      } else if (a.idx_prev) {
+        const int j0 = a.idx_prev[(size_t)b * a.n + qi];
+        if (j0 >= 0 && j0 < a.m) D2[r] = exact_dist2<T, DIM>(tgt + (size_t)j0 * a.cols, qx, qy, qz);
+        thr[r] = filter_threshold(D2[r], gx, gy, gz);
+      } else if (a.bound_in) {
+        float f = FLT_MAX;
+        for (int sl = 0; sl < a.bound_S; ++sl) f = fminf(f, a.bound_in[((size_t)sl * a.N + b) * a.n + qi]);
+        thr[r] = bound_threshold(f, gx, gy, gz);
+      } else {
+        thr[r] = FLT_MAX;
       }
-      thr[r] = filter_threshold(D2[r], qn1[r]);
+      fx[r] = -2.f * gx; fy[r] = -2.f * gy; fz[r] = -2.f * gz;
     }
-    fx[r] = -(float)qx[r]; fy[r] = -(float)qy[r]; fz[r] = -(float)qz[r];
   }
 
   // ---- stream the target slice ----------------------------------------------------------------
@@ -318,33 +396,54 @@ __global__ void __launch_bounds__(NN_THREADS) nn_search_kernel(NNArgs a) {
     const float4* X = reinterpret_cast<const float4*>(sx[buf]);
     const float4* Y = reinterpret_cast<const float4*>(sy[buf]);
     const float4* Z = reinterpret_cast<const float4*>(sz[buf]);
+    const float4* Nn = reinterpret_cast<const float4*>(sn[buf]);
     const int jbase = (tile0 + k) * NN_TILE;
 #pragma unroll 2
-    for (int g = 0; g < NN_TILE / 4; ++g) {
-      const float4 x4 = X[g], y4 = Y[g];
-      const f32x2 xa = pack2(x4.x, x4.y), xb = pack2(x4.z, x4.w);
-      const f32x2 ya = pack2(y4.x, y4.y), yb = pack2(y4.z, y4.w);
-      f32x2 za = 0, zb = 0;
-      if (DIM == 3) { const float4 z4 = Z[g]; za = pack2(z4.x, z4.y); zb = pack2(z4.z, z4.w); }
+    for (int g = 0; g < NN_TILE / NN_G; ++g) {
+      f32x2 xs[4], ys[4], zs[4], ns[4];
+      {
+        const float4 xa = X[2 * g], xb = X[2 * g + 1], ya = Y[2 * g], yb = Y[2 * g + 1];
+        const float4 na = Nn[2 * g], nb = Nn[2 * g + 1];
+        xs[0] = pack2(xa.x, xa.y); xs[1] = pack2(xa.z, xa.w); xs[2] = pack2(xb.x, xb.y); xs[3] = pack2(xb.z, xb.w);
+        ys[0] = pack2(ya.x, ya.y); ys[1] = pack2(ya.z, ya.w); ys[2] = pack2(yb.x, yb.y); ys[3] = pack2(yb.z, yb.w);
+        ns[0] = pack2(na.x, na.y); ns[1] = pack2(na.z, na.w); ns[2] = pack2(nb.x, nb.y); ns[3] = pack2(nb.z, nb.w);
+        if (DIM == 3) {
+          const float4 za = Z[2 * g], zb = Z[2 * g + 1];
+          zs[0] = pack2(za.x, za.y); zs[1] = pack2(za.z, za.w); zs[2] = pack2(zb.x, zb.y); zs[3] = pack2(zb.z, zb.w);
+        }
+      }
+      float mn[NN_R];
+      bool any = false;
 #pragma unroll
       for (int r = 0; r < NN_R; ++r) {
-        const f32x2 nqx = pack2(fx[r], fx[r]), nqy = pack2(fy[r], fy[r]);
-        const f32x2 dxa = add2(xa, nqx), dxb = add2(xb, nqx);
-        const f32x2 dya = add2(ya, nqy), dyb = add2(yb, nqy);
-        f32x2 sa = fma2(dya, dya, mul2(dxa, dxa)), sb = fma2(dyb, dyb, mul2(dxb, dxb));
-        if (DIM == 3) {
-          const f32x2 nqz = pack2(fz[r], fz[r]);
-          const f32x2 dza = add2(za, nqz), dzb = add2(zb, nqz);
-          sa = fma2(dza, dza, sa); sb = fma2(dzb, dzb, sb);
+        const f32x2 qx2 = pack2(fx[r], fx[r]), qy2 = pack2(fy[r], fy[r]);
+        float v[8];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          f32x2 f = fma2(xs[c], qx2, ns[c]);
+          f = fma2(ys[c], qy2, f);
+          if (DIM == 3) { const f32x2 qz2 = pack2(fz[r], fz[r]); f = fma2(zs[c], qz2, f); }
+          unpack2(f, v[2 * c], v[2 * c + 1]);
         }
-        float d0, d1, d2, d3;
-        unpack2(sa, d0, d1); unpack2(sb, d2, d3);
-        const float mn = fminf(min3(d0, d1, d2), d3);
-        if (__builtin_expect(mn <= thr[r], 0)) {
-          // exact path: rare (record-setting candidates and genuine near-ties only)
-          const ExactState st = exact_path<T, DIM>(tgt, a.cols, a.m, jbase + g * 4, d0, d1, d2, d3, thr[r], qx[r],
-                                                   qy[r], qz[r], qn1[r], D2[r], I[r]);
-          D2[r] = st.D2; I[r] = st.I; thr[r] = st.thr;
+        if (BOUND) {
+          thr[r] = min3(min3(v[0], v[1], v[2]), min3(v[3], v[4], v[5]), min3(v[6], v[7], thr[r]));
+        } else {
+          mn[r] = fminf(min3(v[0], v[1], min3(v[2], v[3], v[4])), min3(v[5], v[6], v[7]));
+          any = any || (mn[r] <= thr[r]);
+        }
+      }
+      if (!BOUND && __builtin_expect(any, 0)) {
+        // exact path: rare (record-setting candidates and genuine near-ties only)
+#pragma unroll
+        for (int r = 0; r < NN_R; ++r) {
+          if (mn[r] <= thr[r]) {
+            const int qi = qt * NN_QB + r * NN_THREADS + tid;
+            const int o = g * NN_G;
+            const ExactState st = exact_group<T, DIM>(tgt, a.cols, a.m, jbase + o, src + (size_t)qi * 3, sC,
+                                                      sx[buf] + o, sy[buf] + o, DIM == 3 ? sz[buf] + o : sz[buf],
+                                                      sn[buf] + o, fx[r], fy[r], fz[r], D2[r], I[r], thr[r]);
+            D2[r] = st.D2; I[r] = st.I; thr[r] = st.thr;
+          }
         }
       }
     }
@@ -356,7 +455,8 @@ __global__ void __launch_bounds__(NN_THREADS) nn_search_kernel(NNArgs a) {
     const int qi = qt * NN_QB + r * NN_THREADS + tid;
     if (qi < a.n) {
       const size_t o = ((size_t)s * a.N + b) * a.n + qi;
-      a.pd2[o] = D2[r]; a.pidx[o] = I[r];
+      if (BOUND) a.bound_out[o] = thr[r];
+      else { a.pd2[o] = D2[r]; a.pidx[o] = I[r]; }
     }
   }
 }
@@ -911,7 +1011,25 @@ __global__ void fp32_probe_kernel(int iters, int packed, float* out) {
 template <typename T, int DIM>
 static int launch_nn(const NNArgs& a, const IcpPlan& pl, cudaStream_t st) {
   dim3 grid(pl.qtiles, pl.S, pl.N);
-  nn_search_kernel<T, DIM><<<grid, NN_THREADS, 0, st>>>(a);
+  nn_search_kernel<T, DIM, false><<<grid, NN_THREADS, 0, st>>>(a);
+  return check_launch();
+}
+
+// Cold start: pack every NN_SUB_STRIDE-th target, then the bound pass over that subsample.
+template <typename T, int DIM>
+static int launch_bound(NNArgs a, const IcpPlan& pl, const IcpWorkspace& w, int dim, cudaStream_t st) {
+  const size_t total = (size_t)pl.N * pl.msp;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  pack_targets_kernel<T><<<blocks, 256, 0, st>>>(static_cast<const T*>(a.target), a.cols, pl.N, pl.m, pl.msub, pl.msp,
+                                                  pl.sub_stride, dim, w.sx, w.sy, w.sz, w.sn);
+  int rc = check_launch();
+  if (rc) return rc;
+  a.tx = w.sx; a.ty = w.sy; a.tz = w.sz; a.tn = w.sn;
+  a.mp = pl.msp; a.tiles_per_slice = pl.sub_tiles_per_slice; a.S = pl.S_sub;
+  a.idx_prev = nullptr; a.bound_in = nullptr; a.bound_out = w.bound;
+  dim3 grid(pl.qtiles, pl.S_sub, pl.N);
+  nn_search_kernel<T, DIM, true><<<grid, NN_THREADS, 0, st>>>(a);
   return check_launch();
 }
 
@@ -919,7 +1037,7 @@ static int launch_nn(const NNArgs& a, const IcpPlan& pl, cudaStream_t st) {
 // recorded on the launch stream between the kernel classes; the normal path records nothing.
 struct ForwardProfile {
   std::vector<cudaEvent_t> ev;     // boundaries
-  std::vector<int> cls;            // class of the interval that ENDS at ev[i+1]: 0 nn, 1 step, 2 other
+  std::vector<int> cls;            // class of the interval that ENDS at ev[i+1]: 0 nn, 1 step, 2 other, 3 bound pass
   cudaStream_t st;
   void mark(int c) {
     cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st);
@@ -945,14 +1063,14 @@ static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* s
     const size_t total = (size_t)pl.N * pl.mp;
     int blocks = (int)((total + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
-    pack_targets_kernel<T><<<blocks, 256, 0, st>>>(static_cast<const T*>(target), p->target_cols, pl.N, pl.m, pl.mp,
-                                                    w.tx, w.ty, w.tz);
+    pack_targets_kernel<T><<<blocks, 256, 0, st>>>(static_cast<const T*>(target), p->target_cols, pl.N, pl.m, pl.m,
+                                                    pl.mp, 1, p->dim, w.tx, w.ty, w.tz, w.tn);
     if ((rc = check_launch())) return rc;
   }
 
   NNArgs na;
   na.source = source; na.target = target; na.pose = w.pose;
-  na.tx = w.tx; na.ty = w.ty; na.tz = w.tz;
+  na.tx = w.tx; na.ty = w.ty; na.tz = w.tz; na.tn = w.tn;
   na.frozen = w.frozen; na.counters = w.counters;
   na.pd2 = w.pd2; na.pidx = w.pidx;
   na.N = pl.N; na.n = pl.n; na.m = pl.m; na.mp = pl.mp; na.cols = p->target_cols;
@@ -968,9 +1086,17 @@ static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* s
   sa.const_iter = p->const_iter; sa.save = save; sa.has_weight = p->has_weight && weight;
   sa.tol = p->tolerance; sa.match_thresh = p->match_ratio_thresh;
 
+  na.bound_in = nullptr; na.bound_out = nullptr; na.bound_S = 0;
+  if (pl.sub_stride) {
+    if (prof) prof->mark(2);
+    if ((rc = launch_bound<T, DIM>(na, pl, w, p->dim, st))) return rc;
+    if (prof) prof->mark(3);
+    na.bound_in = w.bound; na.bound_S = pl.S_sub;
+  }
+
   for (int it = 0; it < p->max_iterations; ++it) {
     na.idx_prev = it > 0 ? w.idx_cur : nullptr;
-    if (prof && it == 0) prof->mark(2);
+    if (prof && it == 0 && !pl.sub_stride) prof->mark(2);
     if ((rc = launch_nn<T, DIM>(na, pl, st))) return rc;
     if (prof) prof->mark(0);
     sa.it = it;
@@ -1103,7 +1229,7 @@ int mmb_icp_forward_profiled(const mmb_icp_params* p, const void* source, const 
   ForwardProfile prof;
   int rc = icp_forward_impl(p, source, target, T_init, weight, T_out, pc_out, deltas, weights_hist, costs, converged,
                             iterations, matched_ratio, iters_done, saved, workspace, workspace_bytes, stream, &prof);
-  for (int c = 0; c < 3; ++c) { host_ms[c] = 0.f; host_launches[c] = 0; }
+  for (int c = 0; c < 4; ++c) { host_ms[c] = 0.f; host_launches[c] = 0; }
   if (!prof.ev.empty()) {
     if (cudaEventSynchronize(prof.ev.back()) != cudaSuccess && rc == MMB_OK) rc = MMB_ERR_CUDA;
     for (size_t i = 0; i + 1 < prof.ev.size(); ++i) {
@@ -1156,17 +1282,24 @@ int mmb_nn_search(int32_t N, int32_t n, int32_t m, int32_t target_cols, int32_t 
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
   if (dtype == MMB_F32)
-    pack_targets_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(target), target_cols, N, m, pl.mp, w.tx, w.ty, w.tz);
+    pack_targets_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(target), target_cols, N, m, m, pl.mp, 1, dim, w.tx, w.ty, w.tz, w.tn);
   else
-    pack_targets_kernel<double><<<blocks, 256, 0, st>>>(static_cast<const double*>(target), target_cols, N, m, pl.mp, w.tx, w.ty, w.tz);
+    pack_targets_kernel<double><<<blocks, 256, 0, st>>>(static_cast<const double*>(target), target_cols, N, m, m, pl.mp, 1, dim, w.tx, w.ty, w.tz, w.tn);
   if ((rc = check_launch())) return rc;
   NNArgs na;
   na.source = query; na.target = target; na.pose = w.pose;
-  na.tx = w.tx; na.ty = w.ty; na.tz = w.tz;
+  na.tx = w.tx; na.ty = w.ty; na.tz = w.tz; na.tn = w.tn;
   na.idx_prev = nullptr; na.frozen = nullptr; na.counters = nullptr;
+  na.bound_in = nullptr; na.bound_out = nullptr; na.bound_S = 0;
   na.pd2 = w.pd2; na.pidx = w.pidx;
   na.N = N; na.n = n; na.m = m; na.mp = pl.mp; na.cols = target_cols;
   na.tiles_per_slice = pl.tiles_per_slice; na.S = pl.S;
+  if (pl.sub_stride) {
+    if (dtype == MMB_F32) rc = dim == 2 ? launch_bound<float, 2>(na, pl, w, dim, st) : launch_bound<float, 3>(na, pl, w, dim, st);
+    else rc = dim == 2 ? launch_bound<double, 2>(na, pl, w, dim, st) : launch_bound<double, 3>(na, pl, w, dim, st);
+    if (rc) return rc;
+    na.bound_in = w.bound; na.bound_S = pl.S_sub;
+  }
   if (dtype == MMB_F32) rc = dim == 2 ? launch_nn<float, 2>(na, pl, st) : launch_nn<float, 3>(na, pl, st);
   else rc = dim == 2 ? launch_nn<double, 2>(na, pl, st) : launch_nn<double, 3>(na, pl, st);
   if (rc) return rc;

@@ -79,3 +79,22 @@ def test_clustered_near_ties_fp64_queries():
     q = centers[:, :n] + 1e-3 * torch.randn((N, n, 3), generator=g, dtype=torch.float64)
     idx = nearest_index(q.cuda(), tgt.cuda(), dim=3).cpu()
     assert torch.equal(idx, O.nearest_index(q, tgt, "exact"))
+
+
+def test_cold_start_bound_pass_keeps_every_tie():
+    """m >= 8192 switches on the cold-start bound pass (strided subsample, fp32 only): its threshold
+    must still let every exact tie and near-tie of the full set through, lowest index first."""
+    from mm_masking_b200.dICP.nn import nearest_index
+    g = torch.Generator().manual_seed(21)
+    N, n, m = 2, 600, 20000
+    centers = torch.rand((N, m // 8, 3), generator=g, dtype=torch.float64) * 150 - 75
+    tgt = centers.repeat_interleave(8, dim=1) + 1e-6 * torch.randn((N, m, 3), generator=g, dtype=torch.float64)
+    tgt[:, 8::16] = tgt[:, 0::16]                                        # exact duplicates at a higher index
+    perm = torch.randperm(m, generator=g)
+    tgt = tgt[:, perm]
+    q = centers[:, :n] + 1e-3 * torch.randn((N, n, 3), generator=g, dtype=torch.float64)
+    for dtype in (torch.float64, torch.float32):
+        qq, tt = q.to(dtype), tgt.to(dtype)
+        for slices in (0, 3):
+            idx = nearest_index(qq.cuda(), tt.cuda(), dim=3, nn_slices=slices).cpu()
+            assert torch.equal(idx, O.nearest_index(qq.double(), tt.double(), "exact"))
