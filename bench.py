@@ -179,6 +179,7 @@ def run_ours(args, wl, rank, world, local_rank):
 
     alg = ICP(icp_type="pt2pl", differentiable=True, max_iterations=K, tolerance=1e-5)
     alg.const_iter = True
+    alg.nn_slices = args.nn_slices
     call = dict(trim_dist=5.0, loss_fn={"name": "cauchy", "metric": 1.0}, dim=wl["dim"])
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
 
@@ -246,6 +247,7 @@ def run_ours(args, wl, rank, world, local_rank):
     p.differentiable, p.const_iter, p.use_trim, p.trim_dist = 1, 1, 1, 5.0
     p.loss_kind, p.loss_metric, p.has_weight, p.save_for_backward = _capi.LOSS_CAUCHY, 1.0, 1, 1
     p.tolerance, p.tanh_steepness, p.match_ratio_thresh = 1e-5, 5.0, 0.1
+    p.nn_slices = args.nn_slices
     ws_bytes, sv_bytes = lib.mmb_icp_workspace_bytes(p), lib.mmb_icp_saved_bytes(p)
     f32 = dict(dtype=torch.float32, device=dev)
     bufs = dict(ws=torch.empty(ws_bytes, dtype=torch.uint8, device=dev), sv=torch.empty(sv_bytes, dtype=torch.uint8, device=dev),
@@ -344,6 +346,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--ref-pairs", type=int, default=2, help="pairs per CPU-reference step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--nn-slices", type=int, default=0, help="tuning: target slices per query tile (0 = library default)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     rank = int(os.environ.get("RANK", "0"))

@@ -29,7 +29,7 @@ void set_last_cuda_error(cudaError_t e) {
 constexpr int NN_THREADS = 128;   // threads per NN block
 constexpr int NN_R = 4;           // queries per thread
 constexpr int NN_QB = NN_THREADS * NN_R;
-constexpr int NN_TILE = 1024;     // targets per shared-memory tile
+constexpr int NN_TILE = 512;      // targets per shared-memory tile
 constexpr int STEP_THREADS = 512;
 constexpr int BWD_THREADS = 512;
 constexpr float PAD_COORD = __builtin_huge_valf();   // filter copy padding: never passes the filter
@@ -44,27 +44,19 @@ struct IcpPlan {
   int sub_stride, msub, msp, S_sub, sub_tiles_per_slice;   // strided subsample (0 = no bound pass)
 };
 
+// Target slices per query tile.  Measured on B200 (profiles/r01_nn_slices_sweep.md): short blocks
+// balance best -- the exact path makes block run times uneven -- until the per-query merge of S
+// partial minima in the step kernel starts to cost; ~40 slices is the flat optimum at c3 sizes.
+// With few pairs the split is widened until the grid covers two waves of resident blocks.
 static int pick_slices(int N, int qtiles, int tiles, int requested) {
   if (requested > 0) return requested < tiles ? requested : tiles;
-  // Enough blocks for ~4 resident blocks on each of 148 SMs, in whole waves where possible.
-  const long long slots = 148LL * 4;
+  const long long slots = 148LL * 7;
   const long long units = (long long)N * qtiles;
-  int best = 1; double best_eff = -1.0;
-  for (int S = 1; S <= tiles && S <= 64; ++S) {
-    const int tps = (tiles + S - 1) / S;
-    const int Seff = (tiles + tps - 1) / tps;
-    if (Seff != S) continue;
-    const long long blocks = units * S;
-    const long long waves = (blocks + slots - 1) / slots;
-    // time ~ waves * tiles_per_slice ; ideal ~ units*tiles/slots
-    const double t = (double)waves * tps;
-    const double ideal = (double)units * tiles / (double)slots;
-    double eff = ideal / t;
-    if (blocks < slots) eff = (double)blocks / slots * ((double)tiles / ((double)tps * S));
-    eff -= 0.002 * S;            // partial-merge traffic grows with S
-    if (eff > best_eff) { best_eff = eff; best = S; }
-  }
-  return best;
+  long long S = 40;
+  if (units * S < 2 * slots) S = (2 * slots + units - 1) / units;
+  if (S > tiles) S = tiles;
+  if (S > 128) S = 128;
+  return (int)S;
 }
 
 static IcpPlan make_plan(int N, int n, int m, int icp_type, int dim, int nn_slices) {
@@ -233,6 +225,19 @@ __device__ __forceinline__ float filter_threshold(double D2, float fqx, float fq
   return __double2float_ru(t);
 }
 
+// thr = RU32(D2 - K) with K = |q~|^2 (1 - 2^-19) kept per query: the same value as filter_threshold.
+__device__ __forceinline__ double filter_offset(float fqx, float fqy, float fqz) {
+  const double qn = (double)fqx * fqx + (double)fqy * fqy + (double)fqz * fqz;
+  return qn - qn * FILTER_MARGIN;
+}
+__device__ __forceinline__ float threshold_from_offset(double D2, double K) {
+  if (!(D2 < 1.0e300)) return FLT_MAX;
+  const double t = D2 - K;
+  if (t >= 3.0e38) return FLT_MAX;
+  if (t <= -3.0e38) return -FLT_MAX;
+  return __double2float_ru(t);
+}
+
 // Threshold from the smallest filter value f seen over ANY subset of the targets.  With the
 // two-sided version of the bound above, F >= d^2 - |q~|^2 - 45u |t~|^2 - 11u |q~|^2, and
 // |t| <= |q| + d for the target that attains f, the true nearest distance obeys
@@ -273,30 +278,42 @@ struct ExactState { double D2; int I; float thr; };
 
 constexpr int NN_G = 8;           // targets per filter group (one branch per NN_R x NN_G pairs)
 
-// Cold path of the search: in a group of NN_G targets at least one passed the filter.  Each is
-// re-filtered on its own (the scalar FFMA chain below produces the same bits as the packed one of
-// the streaming loop) and the survivors are compared exactly (fp64 on the caller's own
-// coordinates), lowest index winning ties.  Kept out of line so the streaming loop stays compact
-// in the instruction cache.
+// Cold path of the search: in a group of NN_G targets at least one passed the filter.  The group
+// is re-filtered per target (the scalar FFMA chain below produces the same bits as the packed one
+// of the streaming loop) and the survivors are compared exactly (fp64 on the caller's own
+// coordinates), lowest index winning ties.  The fp64 query and its threshold offset come from the
+// per-thread stash in shared memory (q = stash[0..2], K = stash[3], stride NN_THREADS).  Kept out
+// of line so the streaming loop stays compact in the instruction cache.
 template <typename T, int DIM>
 __device__ __noinline__ ExactState exact_group(const T* __restrict__ tgt, int cols, int m, int j0,
-                                               const T* __restrict__ src_row, const double* __restrict__ P,
                                                const float* __restrict__ gx, const float* __restrict__ gy,
                                                const float* __restrict__ gz, const float* __restrict__ gn, float fx,
-                                               float fy, float fz, double D2, int I, float thr) {
-  double qx, qy, qz;
-  transform_query<T, DIM>(src_row, P, qx, qy, qz);
-#pragma unroll 1
-  for (int c = 0; c < NN_G; ++c) {
-    float f = fmaf(gy[c], fy, fmaf(gx[c], fx, gn[c]));
-    if (DIM == 3) f = fmaf(gz[c], fz, f);
+                                               float fy, float fz, const double* __restrict__ stash, double D2, int I,
+                                               float thr) {
+  const float4 xa = *reinterpret_cast<const float4*>(gx), xb = *reinterpret_cast<const float4*>(gx + 4);
+  const float4 ya = *reinterpret_cast<const float4*>(gy), yb = *reinterpret_cast<const float4*>(gy + 4);
+  const float4 na = *reinterpret_cast<const float4*>(gn), nb = *reinterpret_cast<const float4*>(gn + 4);
+  float f[NN_G] = {fmaf(ya.x, fy, fmaf(xa.x, fx, na.x)), fmaf(ya.y, fy, fmaf(xa.y, fx, na.y)),
+                   fmaf(ya.z, fy, fmaf(xa.z, fx, na.z)), fmaf(ya.w, fy, fmaf(xa.w, fx, na.w)),
+                   fmaf(yb.x, fy, fmaf(xb.x, fx, nb.x)), fmaf(yb.y, fy, fmaf(xb.y, fx, nb.y)),
+                   fmaf(yb.z, fy, fmaf(xb.z, fx, nb.z)), fmaf(yb.w, fy, fmaf(xb.w, fx, nb.w))};
+  if (DIM == 3) {
+    const float4 za = *reinterpret_cast<const float4*>(gz), zb = *reinterpret_cast<const float4*>(gz + 4);
+    f[0] = fmaf(za.x, fz, f[0]); f[1] = fmaf(za.y, fz, f[1]); f[2] = fmaf(za.z, fz, f[2]); f[3] = fmaf(za.w, fz, f[3]);
+    f[4] = fmaf(zb.x, fz, f[4]); f[5] = fmaf(zb.y, fz, f[5]); f[6] = fmaf(zb.z, fz, f[6]); f[7] = fmaf(zb.w, fz, f[7]);
+  }
+  unsigned pass = 0;
+#pragma unroll
+  for (int c = 0; c < NN_G; ++c) pass |= (f[c] <= thr ? 1u : 0u) << c;
+  const double qx = stash[0], qy = stash[NN_THREADS], qz = DIM == 3 ? stash[2 * NN_THREADS] : 0.0;
+  const double K = stash[3 * NN_THREADS];
+  while (pass) {
+    const int c = __ffs(pass) - 1;
+    pass &= pass - 1;
     const int j = j0 + c;
-    if (f <= thr && j < m) {
+    if (j < m) {
       const double e2 = exact_dist2<T, DIM>(tgt + (size_t)j * cols, qx, qy, qz);
-      if (e2 < D2 || (e2 == D2 && j < I)) {
-        D2 = e2; I = j;
-        thr = filter_threshold(D2, (float)qx, (float)qy, DIM == 3 ? (float)qz : 0.f);
-      }
+      if (e2 < D2 || (e2 == D2 && j < I)) { D2 = e2; I = j; thr = threshold_from_offset(D2, K); }
     }
   }
   ExactState st; st.D2 = D2; st.I = I; st.thr = thr;
@@ -332,6 +349,7 @@ __global__ void __launch_bounds__(NN_THREADS) nn_search_kernel(NNArgs a) {
   __shared__ __align__(128) float sn[2][NN_TILE];
   __shared__ __align__(8) uint64_t bar[2];
   __shared__ double sC[12];
+  __shared__ double stash[BOUND ? 1 : NN_R * 4 * NN_THREADS];   // fp64 query + threshold offset, cold path only
 
   const int tid = threadIdx.x;
   if (tid < 12) sC[tid] = a.pose[(size_t)b * 12 + tid];
@@ -371,6 +389,10 @@ __global__ void __launch_bounds__(NN_THREADS) nn_search_kernel(NNArgs a) {
       double qx, qy, qz;
       transform_query<T, DIM>(src + (size_t)qi * 3, sC, qx, qy, qz);
       const float gx = (float)qx, gy = (float)qy, gz = DIM == 3 ? (float)qz : 0.f;
+      if (!BOUND) {
+        double* st = stash + (size_t)r * 4 * NN_THREADS + tid;
+        st[0] = qx; st[NN_THREADS] = qy; st[2 * NN_THREADS] = qz; st[3 * NN_THREADS] = filter_offset(gx, gy, gz);
+      }
       if (BOUND) {
         thr[r] = FLT_MAX;                // running minimum of the filter value
       } else if (a.idx_prev) {
@@ -437,11 +459,11 @@ __global__ void __launch_bounds__(NN_THREADS) nn_search_kernel(NNArgs a) {
 #pragma unroll
         for (int r = 0; r < NN_R; ++r) {
           if (mn[r] <= thr[r]) {
-            const int qi = qt * NN_QB + r * NN_THREADS + tid;
             const int o = g * NN_G;
-            const ExactState st = exact_group<T, DIM>(tgt, a.cols, a.m, jbase + o, src + (size_t)qi * 3, sC,
-                                                      sx[buf] + o, sy[buf] + o, DIM == 3 ? sz[buf] + o : sz[buf],
-                                                      sn[buf] + o, fx[r], fy[r], fz[r], D2[r], I[r], thr[r]);
+            const ExactState st = exact_group<T, DIM>(tgt, a.cols, a.m, jbase + o, sx[buf] + o, sy[buf] + o,
+                                                      DIM == 3 ? sz[buf] + o : sz[buf], sn[buf] + o, fx[r], fy[r],
+                                                      fz[r], stash + (size_t)r * 4 * NN_THREADS + tid, D2[r], I[r],
+                                                      thr[r]);
             D2[r] = st.D2; I[r] = st.I; thr[r] = st.thr;
           }
         }

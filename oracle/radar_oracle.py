@@ -124,3 +124,166 @@ def extract_pc(mask: np.ndarray, res: float, azimuths: np.ndarray, times: np.nda
         out.append(pc.astype(np.float32))
         structure.append((rows.astype(np.int32), bins.astype(np.int32)))
     return (out, structure) if return_structure else out
+
+
+# ---------------------------------------------------------------------------------------------
+# bilinear sampling (`F.grid_sample(mode='bilinear', padding_mode='zeros', align_corners=True)`)
+# ---------------------------------------------------------------------------------------------
+def grid_sample_bilinear(img: np.ndarray, gx: np.ndarray, gy: np.ndarray) -> np.ndarray:
+    """img (H,W); gx, gy normalised coordinates in [-1,1] (x = column, y = row), any shape.
+    Follows ATen's CPU kernel: ix = (gx + 1) * ((W - 1) / 2); taps outside the image contribute 0.
+    """
+    dt = img.dtype.type
+    H, W = img.shape
+    ix = (gx.astype(img.dtype) + dt(1)) * dt((W - 1) / 2)
+    iy = (gy.astype(img.dtype) + dt(1)) * dt((H - 1) / 2)
+    x0 = np.floor(ix); y0 = np.floor(iy)
+    wx1 = ix - x0; wy1 = iy - y0
+    wx0 = dt(1) - wx1; wy0 = dt(1) - wy1
+    out = np.zeros(ix.shape, dtype=img.dtype)
+    for dy, wy in ((0, wy0), (1, wy1)):
+        for dx, wx in ((0, wx0), (1, wx1)):
+            xi = x0 + dx; yi = y0 + dy
+            ok = (xi >= 0) & (xi <= W - 1) & (yi >= 0) & (yi <= H - 1)
+            xs = np.where(ok, xi, 0).astype(np.int64); ys = np.where(ok, yi, 0).astype(np.int64)
+            out = out + np.where(ok, img[ys, xs] * (wx * wy), dt(0))
+    return out
+
+
+def point_to_cart_idx(pc: np.ndarray, cart_resolution=CART_RES, cart_pixel_width=640, min_to_plus_1=False):
+    """`radar_utils.py:374-397`."""
+    u = -pc[:, :, 0] / pc.dtype.type(cart_resolution)
+    v = pc[:, :, 1] / pc.dtype.type(cart_resolution)
+    if min_to_plus_1:
+        return np.stack([v, u], axis=2) / pc.dtype.type(cart_pixel_width - 1) * pc.dtype.type(2)
+    return np.stack([u, v], axis=2) + pc.dtype.type(cart_pixel_width / 2)
+
+
+def extract_weights(mask: np.ndarray, scan_pc: np.ndarray):
+    """`radar_utils.py:108-140`: per-point bilinear sample of the (N,H,W) mask; points with
+    x == 0 and y == 0 (batch padding) get weight 0.  Returns (weights (N,n), stats dict)."""
+    pc = scan_pc.astype(mask.dtype)
+    grid = point_to_cart_idx(pc, cart_pixel_width=640, min_to_plus_1=True)
+    fake = (pc[:, :, 0] == 0) & (pc[:, :, 1] == 0)
+    grid[fake] = -100.0
+    w = np.stack([grid_sample_bilinear(mask[b], grid[b, :, 0], grid[b, :, 1]) for b in range(mask.shape[0])])
+    real = w[~fake]
+    N = w.shape[0]
+    stats = dict(mean_num_non0=float((real > 0.05).sum() / N), mean_w=float(real.mean()), max_w=float(real.max()),
+                 min_w=float(real.min()), diff_mean_num_non0=float((0.5 * np.tanh(5 * real) + 0.5).sum() / N))
+    return w, stats
+
+
+def extract_weights_backward(grad_w: np.ndarray, mask_shape, scan_pc: np.ndarray) -> np.ndarray:
+    """d(sum grad_w * w)/d mask: the adjoint of the bilinear gather (a scatter-add), float64."""
+    N, H, W = mask_shape
+    pc = scan_pc.astype(np.float32)
+    grid = point_to_cart_idx(pc, cart_pixel_width=640, min_to_plus_1=True)
+    fake = (pc[:, :, 0] == 0) & (pc[:, :, 1] == 0)
+    grid[fake] = -100.0
+    out = np.zeros(mask_shape, dtype=np.float64)
+    f = np.float32
+    for b in range(N):
+        ix = (grid[b, :, 0] + f(1)) * f((W - 1) / 2); iy = (grid[b, :, 1] + f(1)) * f((H - 1) / 2)
+        x0 = np.floor(ix); y0 = np.floor(iy)
+        wx1 = ix - x0; wy1 = iy - y0
+        for dy, wy in ((0, f(1) - wy1), (1, wy1)):
+            for dx, wx in ((0, f(1) - wx1), (1, wx1)):
+                xi = x0 + dx; yi = y0 + dy
+                ok = (xi >= 0) & (xi <= W - 1) & (yi >= 0) & (yi <= H - 1)
+                np.add.at(out[b], (yi[ok].astype(np.int64), xi[ok].astype(np.int64)),
+                          (wx * wy)[ok].astype(np.float64) * grad_w[b][ok].astype(np.float64))
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# polar -> Cartesian
+# ---------------------------------------------------------------------------------------------
+def form_cart_range_angle_grid(cart_resolution=CART_RES, cart_pixel_width=640, dtype=np.float32):
+    """`radar_utils.py:399-419` (torch.linspace / sqrt / arctan2 in the working dtype)."""
+    import torch
+    tdt = torch.float32 if dtype == np.float32 else torch.float64
+    if cart_pixel_width % 2 == 0:
+        cmin = (cart_pixel_width / 2 - 0.5) * cart_resolution
+    else:
+        cmin = cart_pixel_width / 2 * cart_resolution
+    coords = torch.linspace(-cmin, cmin, cart_pixel_width, dtype=tdt)
+    Y, X = torch.meshgrid(coords, -1 * coords, indexing='xy')
+    rng = torch.sqrt(Y * Y + X * X)
+    ang = torch.arctan2(Y, X)
+    ang = ang + torch.where(ang < 0, 2.0 * torch.pi, 0.0).to(tdt)
+    return rng.numpy(), ang.numpy()
+
+
+def polar_to_cartesian(fft: np.ndarray, azimuths: np.ndarray, radar_resolution: float, cart_pixel_width=640,
+                       interpolate_crossover=True, fix_wobble=True) -> np.ndarray:
+    """`radar_utils.py:258-336` for a (B,A,R) batch.  Note the reference builds the pixel grid with
+    the DEFAULT Cartesian resolution whatever `cart_resolution` it is given (`:276`)."""
+    dt = fft.dtype.type
+    B, A, R = fft.shape
+    rng, ang = form_cart_range_angle_grid(cart_pixel_width=cart_pixel_width, dtype=fft.dtype)
+    az = azimuths.astype(fft.dtype)
+    out = np.zeros((B, cart_pixel_width, cart_pixel_width), dtype=fft.dtype)
+    for b in range(B):
+        u = (rng - dt(radar_resolution / 2)) / dt(radar_resolution)
+        step = (az[b, -1] - az[b, 0]) / dt(A - 1)
+        v = (ang - az[b, 0]) / step
+        if fix_wobble:
+            c3 = np.searchsorted(az[b], ang.reshape(-1), side='left').reshape(ang.shape)
+            c3[c3 == A] -= 1
+            c2 = c3 - 1
+            c2[c2 < 0] += 1
+            a3 = az[b][c3]; a2 = az[b][c2]
+            diff = ang - a3
+            delta = diff * (diff < 0).astype(fft.dtype) * (c3 > 0).astype(fft.dtype) / (a3 - a2 + dt(1e-14))
+            v = (c3.astype(fft.dtype) + delta).astype(fft.dtype)
+        u = np.where(u < 0, dt(0), u)
+        img = fft[b]
+        if interpolate_crossover:
+            img = np.concatenate([img[-1:], img, img[:1]], axis=0)
+            v = v + dt(1)
+        gx = u / dt(img.shape[1] - 1) * dt(2) - dt(1)
+        gy = v / dt(img.shape[0] - 1) * dt(2) - dt(1)
+        out[b] = grid_sample_bilinear(img, gx, gy)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# K-strongest (C++ specification only)
+# ---------------------------------------------------------------------------------------------
+def kstrongest(fft: np.ndarray, azimuths: np.ndarray, res: float, kstrong=12, threshold2=0.0, threshold3=0.216,
+               minr=2.0, maxr=80.0, range_offset=-0.31):
+    """`detector.inl:39-85` with the ordering fixed as SURVEY.md section 8a note: per azimuth,
+    mean over the bins j = ceil(minr/res) .. (while j < maxr/res), divided by N = maxr/res - minr/res
+    (a double, not the bin count, `:47-61`); keep bins with value >= mean*threshold2 + threshold3;
+    take up to k by descending intensity, ties to the lower bin; rho = j*res + range_offset;
+    (x, y) = (rho cos phi, rho sin phi) (`navtech_extraction_module.cpp:33-39`).
+    Returns per scan (points (P,3) float32, rows int32, bins int32), azimuth-major, selection order.
+    """
+    B, A, R = fft.shape
+    mincol = minr / res
+    maxcol = min(maxr / res, float(R))
+    N = maxcol - mincol
+    j0 = int(np.ceil(mincol))
+    js = np.arange(j0, R)
+    js = js[js < maxcol]
+    out = []
+    for b in range(B):
+        pts, rows, bins = [], [], []
+        for a in range(A):
+            row = fft[b, a, js].astype(np.float64)
+            mean = row.sum() / N
+            thres = mean * threshold2 + threshold3
+            cand = js[row >= thres]
+            if len(cand) == 0:
+                continue
+            vals = fft[b, a, cand]
+            order = np.lexsort((cand, -vals.astype(np.float64)))[:kstrong]
+            for j in cand[order]:
+                rho = np.float32(j * res + range_offset)
+                phi = np.float32(azimuths[b, a])
+                pts.append((rho * np.cos(phi), rho * np.sin(phi), 0.0))
+                rows.append(a); bins.append(j)
+        out.append((np.asarray(pts, dtype=np.float32).reshape(-1, 3), np.asarray(rows, np.int32),
+                    np.asarray(bins, np.int32)))
+    return out
