@@ -128,6 +128,94 @@ int mmb_nn_search(int32_t N, int32_t n, int32_t m, int32_t target_cols, int32_t 
                   int32_t dim, int32_t nn_slices, const void* query, const void* target,
                   int32_t* idx_out, void* workspace, size_t workspace_bytes, void* stream);
 
+
+/* ------------------------------------------------------------------------------------------
+ * Radar preprocessing (mm_masking/radar_utils.py).  dtype = MMB_F32 / MMB_F64 is the working type
+ * of every floating-point buffer of a call.  `scan_u8` != 0: the scan is raw Navtech rows,
+ * (B,A,R+11) uint8 with 11 header bytes per row and value = byte / 255 (radar_utils.py:20-27,
+ * `load_radar`), MMB_F32 only; otherwise (B,A,R) in the working type.
+ * ---------------------------------------------------------------------------------------- */
+
+/* Per-point bilinear sample of the weight mask.  Replaces radar_utils.py:108-126
+ * (`extract_weights` = `point_to_cart_idx(min_to_plus_1=True)` :374-391 + `F.grid_sample(bilinear,
+ * zeros, align_corners=True)`); points with x == 0 and y == 0 are batch padding and get weight 0.
+ *   mask (N,H,W)   pts (N,n,pt_cols) [x,y in columns 0,1]   w_out (N,n) */
+int mmb_sample_weights_fwd(int32_t N, int32_t n, int32_t pt_cols, int32_t H, int32_t W,
+                           int32_t dtype, double cart_res, const void* mask, const void* pts,
+                           void* w_out, void* stream);
+/* Adjoint of the above with respect to the mask (what autograd does for radar_utils.py:126).
+ *   grad_w (N,n)   grad_mask (N,H,W): ACCUMULATED into with atomics, caller zero-fills. */
+int mmb_sample_weights_bwd(int32_t N, int32_t n, int32_t pt_cols, int32_t H, int32_t W,
+                           int32_t dtype, double cart_res, const void* grad_w, const void* pts,
+                           void* grad_mask, void* stream);
+
+/* Polar -> Cartesian resampling.  Replaces radar_utils.py:258-336
+ * (`radar_polar_to_cartesian_diff`).  range_tab / angle_tab: the (width*width) pixel-centre tables
+ * of `form_cart_range_angle_grid` (:399-419), batch-invariant, supplied by the caller.
+ *   scan (B,A,R)   azimuths (B,A)   out (B,width,width) */
+int mmb_polar_to_cart(int32_t B, int32_t A, int32_t R, int32_t width, int32_t dtype,
+                      int32_t scan_u8, const void* scan, const void* azimuths,
+                      const void* range_tab, const void* angle_tab, double radar_res,
+                      int32_t interpolate_crossover, int32_t fix_wobble, void* out, void* stream);
+
+/* GO-CFAR mask.  Replaces radar_utils.py:29-69 (`cfar_mask`). */
+typedef struct mmb_cfar_params {
+  int32_t B, A, R;         /* scans, azimuths per scan, range bins */
+  int32_t dtype;
+  int32_t scan_u8;
+  int32_t width;           /* window width (made odd like radar_utils.py:34) */
+  int32_t guard;
+  int32_t diff;            /* soft tanh mask + hardshrink(0.99) (:64-65) vs x > thres (:67) */
+  double res, minr, maxr, a_thresh, b_thresh, steep_fact;
+} mmb_cfar_params;
+/* the half width and the [mincol, maxcol) column range of radar_utils.py:35-39 (host only) */
+int mmb_cfar_columns(const mmb_cfar_params* p, int32_t* w2, int32_t* mincol, int32_t* maxcol);
+/*   scan (B,A,R)   mask (B,A,R): float32 when !diff (as `torch.where(.., 1.0, 0.0)`), else dtype */
+int mmb_cfar_mask(const mmb_cfar_params* p, const void* scan, void* mask, void* stream);
+
+/* Peak extraction.  Replaces radar_utils.py:71-106 (`extract_pc`, with
+ * `mean_peaks_parallel_fast` :167-185 and `pol_2_cart` :187-195).  Two phases because the
+ * number of points is data dependent: count -> (caller reads totals, allocates) -> write.
+ * fused != 0: the first buffer is the SCAN and the CFAR mask of `cfar` is evaluated on the fly. */
+typedef struct mmb_extract_params {
+  int32_t B, A, R;
+  int32_t dtype;
+  int32_t diff;
+  int32_t fused;
+  double res, steep_fact;
+  mmb_cfar_params cfar;    /* used when fused */
+} mmb_extract_params;
+size_t mmb_extract_workspace_bytes(int32_t B, int32_t A);
+/*   totals (B) int32 device: number of non-zero peak entries per scan (= 2 x points) */
+int mmb_extract_count(const mmb_extract_params* p, const void* mask_or_scan, void* workspace,
+                      size_t workspace_bytes, int32_t* totals, void* stream);
+/*   same workspace as the count call.  ent_val (B,entry_cap) dtype, ent_row (B,entry_cap) int32:
+ *   scratch for the peak entries; azimuths (B,A); T_ab (B,4,4) or NULL;
+ *   points_out (B,out_cap,3): scan b holds totals[b]/2 points, azimuth-major, range ascending. */
+int mmb_extract_write(const mmb_extract_params* p, const void* mask_or_scan, const void* azimuths,
+                      const void* T_ab, void* workspace, size_t workspace_bytes,
+                      int32_t entry_cap, void* ent_val, int32_t* ent_row, int32_t out_cap,
+                      void* points_out, void* stream);
+
+/* K-strongest per azimuth.  Replaces
+ * external/vtr3/main/src/vtr_radar/include/vtr_radar/detector/detector.inl:39-85
+ * (`KStrongest<PointT>::run`) + navtech_extraction_module.cpp:33-39 (`pol2Cart2D`); order within
+ * a row: descending intensity, ties to the lower bin.  Scan is float32 or raw bytes. */
+typedef struct mmb_kstrong_params {
+  int32_t B, A, R;
+  int32_t dtype;           /* azimuths / points dtype */
+  int32_t scan_u8;
+  int32_t k;
+  double res, minr, maxr, threshold2, threshold3, range_offset;
+} mmb_kstrong_params;
+size_t mmb_kstrong_workspace_bytes(const mmb_kstrong_params* p);
+int mmb_kstrong_select(const mmb_kstrong_params* p, const void* scan, void* workspace,
+                       size_t workspace_bytes, int32_t* totals, void* stream);
+/*   points_out (B,out_cap,3); rows_out / bins_out (B,out_cap) int32 or NULL */
+int mmb_kstrong_write(const mmb_kstrong_params* p, const void* azimuths, void* workspace,
+                      size_t workspace_bytes, int32_t out_cap, void* points_out, int32_t* rows_out,
+                      int32_t* bins_out, void* stream);
+
 /* FP32 FMA-pipe probe used by bench.py for the roofline denominator: runs `iters` dependent
  * rounds of 8 independent FFMA (packed=0) or FFMA2 (packed=1) chains per thread on
  * blocks x 256 threads; flops = blocks*256*iters*8*2*(packed?2:1). */

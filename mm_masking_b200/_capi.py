@@ -30,6 +30,27 @@ class IcpParams(C.Structure):
     ]
 
 
+class CfarParams(C.Structure):
+    """mirror of `mmb_cfar_params`"""
+    _fields_ = [("B", C.c_int32), ("A", C.c_int32), ("R", C.c_int32), ("dtype", C.c_int32), ("scan_u8", C.c_int32),
+                ("width", C.c_int32), ("guard", C.c_int32), ("diff", C.c_int32),
+                ("res", C.c_double), ("minr", C.c_double), ("maxr", C.c_double), ("a_thresh", C.c_double),
+                ("b_thresh", C.c_double), ("steep_fact", C.c_double)]
+
+
+class ExtractParams(C.Structure):
+    """mirror of `mmb_extract_params`"""
+    _fields_ = [("B", C.c_int32), ("A", C.c_int32), ("R", C.c_int32), ("dtype", C.c_int32), ("diff", C.c_int32),
+                ("fused", C.c_int32), ("res", C.c_double), ("steep_fact", C.c_double), ("cfar", CfarParams)]
+
+
+class KStrongParams(C.Structure):
+    """mirror of `mmb_kstrong_params`"""
+    _fields_ = [("B", C.c_int32), ("A", C.c_int32), ("R", C.c_int32), ("dtype", C.c_int32), ("scan_u8", C.c_int32),
+                ("k", C.c_int32), ("res", C.c_double), ("minr", C.c_double), ("maxr", C.c_double),
+                ("threshold2", C.c_double), ("threshold3", C.c_double), ("range_offset", C.c_double)]
+
+
 # name -> (restype, argtypes); tests check that every one of these is exported.
 _P = C.c_void_p
 SIGNATURES = {
@@ -44,6 +65,18 @@ SIGNATURES = {
     "mmb_icp_backward": (C.c_int, [C.POINTER(IcpParams)] + [_P] * 11 + [C.c_size_t, _P]),
     "mmb_nn_workspace_bytes": (C.c_size_t, [C.c_int32] * 4),
     "mmb_nn_search": (C.c_int, [C.c_int32] * 7 + [_P] * 4 + [C.c_size_t, _P]),
+    "mmb_sample_weights_fwd": (C.c_int, [C.c_int32] * 6 + [C.c_double, _P, _P, _P, _P]),
+    "mmb_sample_weights_bwd": (C.c_int, [C.c_int32] * 6 + [C.c_double, _P, _P, _P, _P]),
+    "mmb_polar_to_cart": (C.c_int, [C.c_int32] * 6 + [_P] * 4 + [C.c_double, C.c_int32, C.c_int32, _P, _P]),
+    "mmb_cfar_columns": (C.c_int, [C.POINTER(CfarParams)] + [C.POINTER(C.c_int32)] * 3),
+    "mmb_cfar_mask": (C.c_int, [C.POINTER(CfarParams), _P, _P, _P]),
+    "mmb_extract_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "mmb_extract_count": (C.c_int, [C.POINTER(ExtractParams), _P, _P, C.c_size_t, _P, _P]),
+    "mmb_extract_write": (C.c_int, [C.POINTER(ExtractParams), _P, _P, _P, _P, C.c_size_t, C.c_int32, _P, _P,
+                                    C.c_int32, _P, _P]),
+    "mmb_kstrong_workspace_bytes": (C.c_size_t, [C.POINTER(KStrongParams)]),
+    "mmb_kstrong_select": (C.c_int, [C.POINTER(KStrongParams), _P, _P, C.c_size_t, _P, _P]),
+    "mmb_kstrong_write": (C.c_int, [C.POINTER(KStrongParams), _P, _P, C.c_size_t, C.c_int32, _P, _P, _P, _P]),
     "mmb_fp32_probe": (C.c_int, [C.c_int32] * 3 + [_P, _P]),
 }
 

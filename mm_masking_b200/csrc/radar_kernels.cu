@@ -1,0 +1,858 @@
+// Radar preprocessing kernels for sm_100a: per-point bilinear weight sampling (K6, forward and
+// adjoint), polar -> Cartesian resampling (K1), GO-CFAR mask + peak extraction (K2a) and
+// K-strongest extraction (K2b).
+//
+// What is computed follows mm_masking/radar_utils.py of the reference (and, for K-strongest,
+// external/vtr3/main/src/vtr_radar/include/vtr_radar/detector/detector.inl:39-85); see
+// include/mm_masking_b200.h for the per-function mapping.  How it is computed does not: the
+// reference builds these from dozens of ATen launches (two Python loops of 1 198 `torch.sum`
+// calls for the CFAR windows, a (B,640,400) expanded searchsorted, per-sample `nonzero`), here each
+// stage is one pass over the scan in HBM order with the row staged in shared memory.
+#include "mmb_common.cuh"
+
+#include <type_traits>
+
+namespace mmb {
+
+// All of these kernels are bound by HBM traffic; grids are sized in whole rows / pixels.
+constexpr int ROW_THREADS = 256;
+
+// Inputs come as fp32, fp64 or raw Navtech bytes (radar_utils.py:20-27: 11 header bytes per row,
+// value = byte / 255 in fp32).
+enum { IN_F32 = 0, IN_F64 = 1, IN_U8 = 2 };
+
+template <typename T> struct Scan {
+  const void* base; int kind; size_t row_stride;      // elements (bytes for u8) between azimuth rows
+  __device__ __forceinline__ T at(size_t row, int col) const {
+    if (kind == IN_F32) return (T) static_cast<const float*>(base)[row * row_stride + col];
+    if (kind == IN_F64) return (T) static_cast<const double*>(base)[row * row_stride + col];
+    return (T)__fdiv_rn((float)static_cast<const uint8_t*>(base)[row * row_stride + 11 + col], 255.0f);
+  }
+};
+
+template <typename T> __device__ __forceinline__ T t_floor(T v);
+template <> __device__ __forceinline__ float t_floor<float>(float v) { return floorf(v); }
+template <> __device__ __forceinline__ double t_floor<double>(double v) { return floor(v); }
+template <typename T> __device__ __forceinline__ T t_tanh(T v);
+template <> __device__ __forceinline__ float t_tanh<float>(float v) { return tanhf(v); }
+template <> __device__ __forceinline__ double t_tanh<double>(double v) { return tanh(v); }
+
+// Unfused arithmetic in the working type, so that products and sums round where ATen's do.
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float div_rn(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ double div_rn(double a, double b) { return __ddiv_rn(a, b); }
+
+// ---------------------------------------------------------------------------------------------
+// bilinear taps of `grid_sample(mode='bilinear', padding_mode='zeros', align_corners=True)`
+// (ATen CPU kernel: ix = (gx + 1) * ((W - 1) / 2); weights nw = (1-fy)(1-fx) ...; taps outside
+// the image contribute 0)
+// ---------------------------------------------------------------------------------------------
+template <typename T> struct Taps { int x0, y0; T nw, ne, sw, se; };
+
+template <typename T>
+__device__ __forceinline__ Taps<T> bilinear_taps(T gx, T gy, int W, int H) {
+  const T ix = mul_rn(add_rn(gx, (T)1), (T)(W - 1) / (T)2);
+  const T iy = mul_rn(add_rn(gy, (T)1), (T)(H - 1) / (T)2);
+  const T xw = t_floor(ix), yn = t_floor(iy);
+  const T w = add_rn(ix, -xw), e = add_rn((T)1, -w);
+  const T n = add_rn(iy, -yn), s = add_rn((T)1, -n);
+  Taps<T> t;
+  // keep far-out-of-range coordinates (the -100 of padded points) inside int range
+  t.x0 = (int)fmax(fmin((double)xw, 2.0e9), -2.0e9);
+  t.y0 = (int)fmax(fmin((double)yn, 2.0e9), -2.0e9);
+  t.nw = mul_rn(s, e); t.ne = mul_rn(s, w); t.sw = mul_rn(n, e); t.se = mul_rn(n, w);
+  return t;
+}
+
+__device__ __forceinline__ bool inside(int x, int y, int W, int H) { return x >= 0 && x < W && y >= 0 && y < H; }
+
+// ---------------------------------------------------------------------------------------------
+// K6: per-point weight sampling (radar_utils.py:108-126) and its adjoint
+// ---------------------------------------------------------------------------------------------
+// grid = (v, u) * 2 / (W - 1) with u = -x / cart_res, v = y / cart_res (radar_utils.py:374-391);
+// points with x == 0 and y == 0 are batch padding and sample at (-100, -100) -> 0 (:118-122).
+template <typename T>
+__device__ __forceinline__ void point_grid(const T* __restrict__ p, T cart_res, int W, T& gx, T& gy) {
+  const T x = p[0], y = p[1];
+  if (x == (T)0 && y == (T)0) { gx = (T)-100; gy = (T)-100; return; }
+  const T u = div_rn(-x, cart_res), v = div_rn(y, cart_res);
+  gx = mul_rn(div_rn(v, (T)(W - 1)), (T)2);
+  gy = mul_rn(div_rn(u, (T)(W - 1)), (T)2);
+}
+
+template <typename T>
+__global__ void sample_weights_kernel(const T* __restrict__ mask, const T* __restrict__ pts, int pt_cols, int N, int n,
+                                      int H, int W, T cart_res, T* __restrict__ out) {
+  const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (size_t)N * n) return;
+  const int b = (int)(g / n);
+  T gx, gy;
+  point_grid<T>(pts + g * pt_cols, cart_res, W, gx, gy);
+  const Taps<T> t = bilinear_taps<T>(gx, gy, W, H);
+  const T* img = mask + (size_t)b * H * W;
+  T acc = (T)0;
+  if (inside(t.x0, t.y0, W, H)) acc = mul_rn(img[(size_t)t.y0 * W + t.x0], t.nw);
+  if (inside(t.x0 + 1, t.y0, W, H)) acc = add_rn(acc, mul_rn(img[(size_t)t.y0 * W + t.x0 + 1], t.ne));
+  if (inside(t.x0, t.y0 + 1, W, H)) acc = add_rn(acc, mul_rn(img[(size_t)(t.y0 + 1) * W + t.x0], t.sw));
+  if (inside(t.x0 + 1, t.y0 + 1, W, H)) acc = add_rn(acc, mul_rn(img[(size_t)(t.y0 + 1) * W + t.x0 + 1], t.se));
+  out[g] = acc;
+}
+
+// grad_mask must be zero-filled by the caller; taps are accumulated with atomics (as ATen's own
+// grid_sample backward does), so colliding taps sum in an unspecified order.
+template <typename T>
+__global__ void sample_weights_bwd_kernel(const T* __restrict__ grad_w, const T* __restrict__ pts, int pt_cols, int N,
+                                          int n, int H, int W, T cart_res, T* __restrict__ grad_mask) {
+  const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (size_t)N * n) return;
+  const int b = (int)(g / n);
+  T gx, gy;
+  point_grid<T>(pts + g * pt_cols, cart_res, W, gx, gy);
+  const Taps<T> t = bilinear_taps<T>(gx, gy, W, H);
+  T* img = grad_mask + (size_t)b * H * W;
+  const T go = grad_w[g];
+  if (inside(t.x0, t.y0, W, H)) atomicAdd(img + (size_t)t.y0 * W + t.x0, mul_rn(go, t.nw));
+  if (inside(t.x0 + 1, t.y0, W, H)) atomicAdd(img + (size_t)t.y0 * W + t.x0 + 1, mul_rn(go, t.ne));
+  if (inside(t.x0, t.y0 + 1, W, H)) atomicAdd(img + (size_t)(t.y0 + 1) * W + t.x0, mul_rn(go, t.sw));
+  if (inside(t.x0 + 1, t.y0 + 1, W, H)) atomicAdd(img + (size_t)(t.y0 + 1) * W + t.x0 + 1, mul_rn(go, t.se));
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1: polar -> Cartesian (radar_utils.py:258-336)
+// ---------------------------------------------------------------------------------------------
+// One thread per output pixel.  range_tab / angle_tab are the (width x width) pixel-centre tables of
+// form_cart_range_angle_grid (radar_utils.py:399-419); they depend only on the image width and the
+// dtype and are computed once on the host with the reference's own torch calls, so that the only
+// arithmetic done here is the per-scan part.  The scan's azimuth table sits in shared memory for the
+// searchsorted of the "wobble fix" (:295-309).
+struct PolarArgs {
+  const void* scan; int scan_kind; size_t scan_row_stride; size_t scan_batch_stride;   // (B,A,R)
+  const void* azimuths;          // (B,A) working dtype
+  const void* range_tab; const void* angle_tab;   // (width*width)
+  void* out;                     // (B,width,width)
+  int B, A, R, width;
+  int interpolate_crossover, fix_wobble;
+  double radar_res;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(ROW_THREADS) polar_to_cart_kernel(PolarArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* saz = reinterpret_cast<T*>(smem_raw);
+  const int b = blockIdx.y;
+  const T* az = static_cast<const T*>(a.azimuths) + (size_t)b * a.A;
+  for (int i = threadIdx.x; i < a.A; i += blockDim.x) saz[i] = az[i];
+  __syncthreads();
+
+  const int npix = a.width * a.width;
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= npix) return;
+  const T range = static_cast<const T*>(a.range_tab)[pix];
+  const T angle = static_cast<const T*>(a.angle_tab)[pix];
+  const T res = (T)a.radar_res, half = (T)(a.radar_res / 2);
+
+  T u = div_rn(add_rn(range, -half), res);                                   // :288
+  T v;
+  if (a.fix_wobble) {
+    int lo = 0, hi = a.A;                    // searchsorted, side = left: first i with az[i] >= angle
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (saz[mid] < angle) lo = mid + 1; else hi = mid;
+    }
+    int c3 = lo;
+    if (c3 == a.A) c3 -= 1;                                                  // :300
+    int c2 = c3 - 1;
+    if (c2 < 0) c2 += 1;                                                     // :302
+    const T a3 = saz[c3], a2 = saz[c2];
+    const T diff = add_rn(angle, -a3);
+    T num = mul_rn(diff, diff < (T)0 ? (T)1 : (T)0);
+    num = mul_rn(num, c3 > 0 ? (T)1 : (T)0);
+    const T delta = div_rn(num, add_rn(add_rn(a3, -a2), (T)1e-14));          // :308
+    v = add_rn((T)c3, delta);
+  } else {
+    const T step = div_rn(add_rn(saz[a.A - 1], -saz[0]), (T)(a.A - 1));      // :286
+    v = div_rn(add_rn(angle, -saz[0]), step);                                // :290
+  }
+  if (u < (T)0) u = (T)0;                                                    // :314
+  int H = a.A;
+  if (a.interpolate_crossover) { H = a.A + 2; v = add_rn(v, (T)1); }         // :317-319
+  const T gx = add_rn(mul_rn(div_rn(u, (T)(a.R - 1)), (T)2), (T)-1);         // :322
+  const T gy = add_rn(mul_rn(div_rn(v, (T)(H - 1)), (T)2), (T)-1);           // :323
+  const Taps<T> t = bilinear_taps<T>(gx, gy, a.R, H);
+
+  Scan<T> sc; sc.base = a.scan; sc.kind = a.scan_kind; sc.row_stride = a.scan_row_stride;
+  const size_t row0 = (size_t)b * a.A;
+  auto fetch = [&](int x, int y) -> T {
+    if (!inside(x, y, a.R, H)) return (T)0;
+    int r = y;
+    if (a.interpolate_crossover) r = y == 0 ? a.A - 1 : (y == a.A + 1 ? 0 : y - 1);   // wrapped pad rows
+    return sc.at(row0 + r, x);
+  };
+  T acc = mul_rn(fetch(t.x0, t.y0), t.nw);
+  acc = add_rn(acc, mul_rn(fetch(t.x0 + 1, t.y0), t.ne));
+  acc = add_rn(acc, mul_rn(fetch(t.x0, t.y0 + 1), t.sw));
+  acc = add_rn(acc, mul_rn(fetch(t.x0 + 1, t.y0 + 1), t.se));
+  static_cast<T*>(a.out)[(size_t)b * npix + pix] = acc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// block-wide exclusive scan of one value per thread (blockDim.x <= 1024, multiple of 32)
+// ---------------------------------------------------------------------------------------------
+template <typename V>
+__device__ __forceinline__ V block_exclusive_scan(V x, V* warp_tot /* >= 33 entries */, V& total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  V inc = x;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const V y = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += y;
+  }
+  __syncthreads();                              // warp_tot may still be read from a previous call
+  if (lane == 31) warp_tot[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    V w = lane < nwarp ? warp_tot[lane] : V(0);
+    V winc = w;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const V y = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += y;
+    }
+    if (lane < nwarp) warp_tot[lane] = winc - w;   // exclusive prefix of the warp totals
+    if (lane == 31) warp_tot[32] = winc;           // block total (lanes >= nwarp carry the last sum)
+  }
+  __syncthreads();
+  total = warp_tot[32];
+  return warp_tot[warp] + inc - x;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2a part 1: GO-CFAR mask (radar_utils.py:29-69)
+// ---------------------------------------------------------------------------------------------
+// One block per azimuth row.  The window sums of :46-53 are differences of an fp64 prefix sum of
+// the row staged in shared memory: exact for uint8-derived scans whatever the order (a sum of 50
+// such values needs < 40 bits), so the mask does not depend on how a host library orders a
+// float32 sum.  thres = a * max(left, right) / w2 + b inside [mincol, maxcol), 1000 outside (:55-60).
+struct CfarArgs {
+  const void* scan; int scan_kind; size_t scan_row_stride;
+  void* mask;                    // (rows, R): float when !diff, working dtype when diff
+  int rows, R;
+  int w2, guard, mincol, maxcol; // radar_utils.py:34-40
+  int lo, hi;                    // columns [lo, hi) cover every window: staged in shared memory
+  double a_thresh, b_thresh, steep;
+  int diff;
+};
+
+// Stage x[lo, hi) as an inclusive fp64 prefix sum: pre[0] = 0, pre[i + 1] = x[lo] + ... + x[lo + i].
+template <typename T>
+__device__ __forceinline__ void stage_prefix(const Scan<T>& sc, size_t row, int lo, int hi, double* pre, double* wt) {
+  const int len = hi - lo;
+  for (int i = threadIdx.x; i < len; i += blockDim.x) pre[i + 1] = (double)sc.at(row, lo + i);
+  if (threadIdx.x == 0) pre[0] = 0.0;
+  __syncthreads();
+  const int chunk = (len + blockDim.x - 1) / blockDim.x;
+  const int s = threadIdx.x * chunk, e = min(s + chunk, len);
+  double sum = 0.0;
+  for (int i = s; i < e; ++i) sum += pre[i + 1];
+  double total;
+  double run = block_exclusive_scan<double>(sum, wt, total);
+  for (int i = s; i < e; ++i) { run += pre[i + 1]; pre[i + 1] = run; }
+  __syncthreads();
+}
+
+__device__ __forceinline__ double cfar_threshold_at(const CfarArgs& a, const double* pre, int j) {
+  if (j < a.mincol || j >= a.maxcol) return 1000.0;
+  auto P = [&](int k) { return pre[min(k, a.hi) - a.lo]; };     // slices past the row end are truncated
+  const double left = P(j - a.guard) - P(j - a.w2 - a.guard);
+  const double right = P(j + a.w2 + a.guard + 1) - P(j + a.guard + 1);
+  return a.a_thresh * (fmax(left, right) / (double)a.w2) + a.b_thresh;
+}
+
+template <typename T>
+__device__ __forceinline__ T cfar_mask_value(const CfarArgs& a, T x, double thres) {
+  if (!a.diff) return (double)x > thres ? (T)1 : (T)0;                                   // :67
+  const T soft = add_rn(mul_rn((T)0.5, t_tanh<T>(add_rn(mul_rn((T)a.steep, add_rn(x, -(T)thres)), (T)2.5))), (T)0.5);   // :64
+  return (soft > (T)0.99 || soft < (T)-0.99) ? soft : (T)0;                              // hardshrink :65
+}
+
+template <typename T, bool DIFF>
+__global__ void __launch_bounds__(ROW_THREADS) cfar_mask_kernel(CfarArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* pre = reinterpret_cast<double*>(smem_raw);
+  __shared__ double wt[33];
+  const size_t row = blockIdx.x;
+  Scan<T> sc; sc.base = a.scan; sc.kind = a.scan_kind; sc.row_stride = a.scan_row_stride;
+  stage_prefix<T>(sc, row, a.lo, a.hi, pre, wt);
+  typedef typename std::conditional<DIFF, T, float>::type OT;
+  OT* out = static_cast<OT*>(a.mask) + row * a.R;
+  for (int j = threadIdx.x; j < a.R; j += blockDim.x) {
+    OT m = (OT)0;
+    if (j >= a.mincol && j < a.maxcol) m = (OT)cfar_mask_value<T>(a, sc.at(row, j), cfar_threshold_at(a, pre, j));
+    out[j] = m;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2a part 2: peak extraction (radar_utils.py:71-106, 167-195)
+// ---------------------------------------------------------------------------------------------
+// arr[k] = (res * k) * mask[k]; the "peak" array is
+//     v[k] = arr[k] * z[k+1] + arr[k+1] * z[k]   (k < R-1),  v[R-1] = 0,
+// z = (arr == 0) (non-diff) or 1 - tanh(steep * arr) (diff).  The non-zero v of the flattened
+// scan, in order, are paired (2i, 2i+1) and averaged into (rho, phi) -> (rho cos phi, rho sin phi, 0).
+// Three passes, all one block per azimuth row with arr staged in shared memory:
+//   count:  non-zero v per row                       -> counts (B*A)
+//   offsets: exclusive scan of the A counts per scan -> offsets (B, A+1)      [one block per scan]
+//   write:  (value, row) of every non-zero v at its flattened ordinal; then one thread per point.
+// The row source is either a mask tensor (the reference's extract_pc signature) or the CFAR mask
+// evaluated on the fly from the scan (fused cfar + extraction: the mask is never written).
+struct PeakArgs {
+  // mask source
+  const void* mask; size_t mask_row_stride;        // (rows, R) working dtype, or nullptr for the fused source
+  CfarArgs cfar;                                    // fused source (non-diff or diff)
+  int rows, A, R;
+  float res;
+  int diff; double steep;
+  int* counts;                  // (rows)
+  const int* offsets;           // (B, A+1)
+  void* ent_val; int* ent_row;  // (B, cap) entries
+  int cap;
+};
+
+template <typename T, bool FUSED>
+__device__ __forceinline__ void stage_arr(const PeakArgs& a, size_t row, T* arr, double* pre, double* wt) {
+  if (FUSED) {
+    Scan<T> sc; sc.base = a.cfar.scan; sc.kind = a.cfar.scan_kind; sc.row_stride = a.cfar.scan_row_stride;
+    stage_prefix<T>(sc, row, a.cfar.lo, a.cfar.hi, pre, wt);
+    for (int k = threadIdx.x; k < a.R; k += blockDim.x) {
+      T m = (T)0;
+      if (k >= a.cfar.mincol && k < a.cfar.maxcol) {
+        m = cfar_mask_value<T>(a.cfar, sc.at(row, k), cfar_threshold_at(a.cfar, pre, k));
+      }
+      arr[k] = mul_rn((T)__fmul_rn(a.res, (float)k), m);
+    }
+  } else {
+    const T* mrow = static_cast<const T*>(a.mask) + row * a.mask_row_stride;
+    for (int k = threadIdx.x; k < a.R; k += blockDim.x) arr[k] = mul_rn((T)__fmul_rn(a.res, (float)k), mrow[k]);
+  }
+  __syncthreads();
+}
+
+template <typename T>
+__device__ __forceinline__ T peak_value(const PeakArgs& a, const T* arr, int k) {
+  if (k >= a.R - 1) return (T)0;
+  const T x0 = arr[k], x1 = arr[k + 1];
+  T z0, z1;
+  if (a.diff) {
+    z0 = add_rn((T)1, -t_tanh<T>(mul_rn((T)a.steep, x0)));
+    z1 = add_rn((T)1, -t_tanh<T>(mul_rn((T)a.steep, x1)));
+  } else {
+    z0 = x0 == (T)0 ? (T)1 : (T)0;
+    z1 = x1 == (T)0 ? (T)1 : (T)0;
+  }
+  return add_rn(mul_rn(x0, z1), mul_rn(x1, z0));
+}
+
+template <typename T, bool FUSED, bool WRITE>
+__global__ void __launch_bounds__(ROW_THREADS) peak_rows_kernel(PeakArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* pre = reinterpret_cast<double*>(smem_raw);                       // fused source only
+  T* arr = reinterpret_cast<T*>(smem_raw + (FUSED ? (size_t)(a.cfar.hi - a.cfar.lo + 1) * sizeof(double) : 0));
+  __shared__ double wt[33];
+  __shared__ int wi[33];
+  const size_t row = blockIdx.x;
+  stage_arr<T, FUSED>(a, row, arr, pre, wt);
+
+  // each thread owns a contiguous chunk so that ordinals follow the range order
+  const int chunk = (a.R + blockDim.x - 1) / blockDim.x;
+  const int s = threadIdx.x * chunk, e = min(s + chunk, a.R);
+  int cnt = 0;
+  for (int k = s; k < e; ++k) cnt += peak_value<T>(a, arr, k) != (T)0 ? 1 : 0;
+  int total;
+  int pos = block_exclusive_scan<int>(cnt, wi, total);
+  if (!WRITE) {
+    if (threadIdx.x == 0) a.counts[row] = total;
+    return;
+  }
+  const int b = (int)(row / a.A), r = (int)(row % a.A);
+  pos += a.offsets[(size_t)b * (a.A + 1) + r];
+  T* ev = static_cast<T*>(a.ent_val) + (size_t)b * a.cap;
+  int* er = a.ent_row + (size_t)b * a.cap;
+  for (int k = s; k < e; ++k) {
+    const T v = peak_value<T>(a, arr, k);
+    if (v != (T)0) {
+      if (pos < a.cap) { ev[pos] = v; er[pos] = r; }
+      ++pos;
+    }
+  }
+}
+
+// offsets (B, A+1): exclusive scan of each scan's row counts; offsets[b][A] = number of entries.
+__global__ void row_offsets_kernel(const int* __restrict__ counts, int A, int* __restrict__ offsets,
+                                   int* __restrict__ totals) {
+  __shared__ int wi[33];
+  const int b = blockIdx.x;
+  int carry = 0;
+  for (int base = 0; base < A; base += blockDim.x) {
+    const int r = base + threadIdx.x;
+    const int c = r < A ? counts[(size_t)b * A + r] : 0;
+    int total;
+    const int ex = block_exclusive_scan<int>(c, wi, total);
+    if (r < A) offsets[(size_t)b * (A + 1) + r] = carry + ex;
+    carry += total;
+  }
+  if (threadIdx.x == 0) {
+    offsets[(size_t)b * (A + 1) + A] = carry;
+    if (totals) totals[b] = carry;
+  }
+}
+
+// One thread per point: entries (2i, 2i+1) -> (rho, phi) -> xyz (radar_utils.py:96-104, 187-195).
+template <typename T>
+__global__ void peak_points_kernel(const T* __restrict__ ent_val, const int* __restrict__ ent_row,
+                                   const int* __restrict__ offsets, const T* __restrict__ azimuths,
+                                   const T* __restrict__ T_ab, int A, int cap, int out_cap, T* __restrict__ out) {
+  const int b = blockIdx.y;
+  const int npts = offsets[(size_t)b * (A + 1) + A] / 2;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npts || i >= out_cap || 2 * i + 1 >= cap) return;
+  const T* ev = ent_val + (size_t)b * cap;
+  const int* er = ent_row + (size_t)b * cap;
+  const T rho = div_rn(add_rn(ev[2 * i + 1], ev[2 * i]), (T)2);
+  const T phi = div_rn(add_rn(azimuths[(size_t)b * A + er[2 * i + 1]], azimuths[(size_t)b * A + er[2 * i]]), (T)2);
+  // cos/sin: correctly rounded (evaluated in fp64, rounded once), then the reference's product;
+  // the host libraries the reference runs on differ from each other by an ulp here.
+  T x = mul_rn(rho, (T)cos((double)phi)), y = mul_rn(rho, (T)sin((double)phi)), z = (T)0;
+  if (T_ab) {
+    const T* M = T_ab + (size_t)b * 16;
+    const T xx = add_rn(add_rn(mul_rn(M[0], x), mul_rn(M[1], y)), M[3]);
+    const T yy = add_rn(add_rn(mul_rn(M[4], x), mul_rn(M[5], y)), M[7]);
+    const T zz = add_rn(add_rn(mul_rn(M[8], x), mul_rn(M[9], y)), M[11]);
+    x = xx; y = yy; z = zz;
+  }
+  T* o = out + ((size_t)b * out_cap + i) * 3;
+  o[0] = x; o[1] = y; o[2] = z;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2b: K-strongest per azimuth (vtr_radar detector.inl:39-85, KStrongest<PointT>::run)
+// ---------------------------------------------------------------------------------------------
+// Per row: mean over bins [j0, j1) accumulated in double and divided by the DOUBLE N = maxcol - mincol
+// (not the bin count, detector.inl:47-61); thres = mean * t2 + t3; among bins with value >= thres
+// take up to k by descending value, ties to the lower bin (the C++ comparator is ill-typed and its
+// order implementation-defined, SURVEY.md 8a note; this is the intended order); rho = float(j) * res
+// + range_offset; (x, y) = rho (cos phi, sin phi) (navtech_extraction_module.cpp:33-39).
+struct KStrongArgs {
+  const void* scan; int scan_kind; size_t scan_row_stride;
+  int rows, A, R, j0, j1, k;
+  double N, t2, t3;
+  int* sel_bin;                 // (rows, k)
+  int* counts;                  // (rows)
+};
+
+__device__ __forceinline__ unsigned int ordered_bits(float v) {
+  const unsigned int u = __float_as_uint(v);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+__global__ void __launch_bounds__(ROW_THREADS) kstrong_rows_kernel(KStrongArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float* val = reinterpret_cast<float*>(smem_raw);
+  __shared__ double wd[33];
+  __shared__ unsigned long long wk[33];
+  const size_t row = blockIdx.x;
+  Scan<float> sc; sc.base = a.scan; sc.kind = a.scan_kind; sc.row_stride = a.scan_row_stride;
+  const int len = a.j1 - a.j0;
+  double sum = 0.0;
+  for (int i = threadIdx.x; i < len; i += blockDim.x) {
+    const float v = sc.at(row, a.j0 + i);
+    val[i] = v;
+    sum += (double)v;
+  }
+  sum = warp_sum(sum);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  if (lane == 0) wd[warp] = sum;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0;
+    for (int w = 0; w < nwarp; ++w) s += wd[w];
+    wd[32] = (s / a.N) * a.t2 + a.t3;
+  }
+  __syncthreads();
+  const double thres = wd[32];
+
+  int taken = 0;
+  for (int round = 0; round < a.k; ++round) {
+    unsigned long long best = 0ull;
+    for (int i = threadIdx.x; i < len; i += blockDim.x) {
+      const float v = val[i];
+      if ((double)v >= thres) {
+        const unsigned long long key = ((unsigned long long)ordered_bits(v) << 32) | (unsigned int)(0x7fffffff - i);
+        best = key > best ? key : best;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const unsigned long long y = __shfl_xor_sync(0xffffffffu, best, o);
+      best = y > best ? y : best;
+    }
+    if (lane == 0) wk[warp] = best;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      unsigned long long bb = 0ull;
+      for (int w = 0; w < nwarp; ++w) bb = wk[w] > bb ? wk[w] : bb;
+      wk[32] = bb;
+      if (bb) {
+        const int i = 0x7fffffff - (int)(bb & 0xffffffffu);
+        a.sel_bin[row * a.k + round] = a.j0 + i;
+        val[i] = -__builtin_huge_valf();          // taken; -inf never passes `>= thres`
+      }
+    }
+    __syncthreads();
+    if (!wk[32]) break;
+    ++taken;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) a.counts[row] = taken;
+}
+
+template <typename T>
+__global__ void kstrong_points_kernel(const int* __restrict__ sel_bin, const int* __restrict__ counts,
+                                      const int* __restrict__ offsets, const T* __restrict__ azimuths, int A, int k,
+                                      float res, double range_offset, int out_cap, T* __restrict__ out,
+                                      int* __restrict__ out_row, int* __restrict__ out_bin) {
+  const int b = blockIdx.y;
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= A * k) return;
+  const int r = g / k, slot = g % k;
+  const size_t row = (size_t)b * A + r;
+  if (slot >= counts[row]) return;
+  const int pos = offsets[(size_t)b * (A + 1) + r] + slot;
+  if (pos >= out_cap) return;
+  const int j = sel_bin[row * k + slot];
+  const float rho = (float)((double)__fmul_rn((float)j, res) + range_offset);
+  const T phi = azimuths[row];
+  const size_t o = (size_t)b * out_cap + pos;
+  out[o * 3 + 0] = mul_rn((T)rho, (T)cos((double)phi));
+  out[o * 3 + 1] = mul_rn((T)rho, (T)sin((double)phi));
+  out[o * 3 + 2] = (T)0;
+  if (out_row) out_row[o] = r;
+  if (out_bin) out_bin[o] = j;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host-side dispatch
+// ---------------------------------------------------------------------------------------------
+static int scan_kind_of(int32_t dtype, int32_t scan_u8) { return scan_u8 ? IN_U8 : (dtype == MMB_F64 ? IN_F64 : IN_F32); }
+
+static int fill_cfar(const mmb_cfar_params* p, const void* scan, CfarArgs& c) {
+  if (!p) return MMB_ERR_NULL_POINTER;
+  if (p->B <= 0 || p->A <= 0 || p->R <= 1) return MMB_ERR_INVALID_SHAPE;
+  if (p->dtype != MMB_F32 && p->dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  if (p->scan_u8 && p->dtype != MMB_F32) return MMB_ERR_UNSUPPORTED;
+  if (!(p->res > 0.0)) return MMB_ERR_INVALID_SHAPE;
+  int width = p->width;
+  if (width % 2 == 0) width += 1;                                            // radar_utils.py:34
+  c.w2 = width / 2; c.guard = p->guard;
+  if (c.w2 <= 0 || c.guard < 0) return MMB_ERR_INVALID_SHAPE;
+  const double lo = p->minr / p->res + c.w2 + c.guard + 1, hi = p->maxr / p->res - c.w2 - c.guard;
+  c.mincol = lo < 0 ? 0 : (int)lo;                                           // max(0, int(...)) :38
+  c.maxcol = (int)hi;
+  if (c.maxcol > p->R) c.maxcol = p->R;                                      // min(R, int(...)) :39
+  if (c.maxcol < c.mincol) c.maxcol = c.mincol;
+  c.lo = c.mincol - c.w2 - c.guard;
+  if (c.lo < 0) return MMB_ERR_UNSUPPORTED;        // a negative slice start wraps around in the reference
+  c.hi = c.maxcol + c.w2 + c.guard + 1;
+  if (c.hi > p->R) c.hi = p->R;
+  if (c.hi < c.lo) c.hi = c.lo;
+  c.scan = scan; c.scan_kind = scan_kind_of(p->dtype, p->scan_u8);
+  c.scan_row_stride = p->scan_u8 ? (size_t)p->R + 11 : (size_t)p->R;
+  c.rows = p->B * p->A; c.R = p->R;
+  c.a_thresh = p->a_thresh; c.b_thresh = p->b_thresh; c.steep = p->steep_fact; c.diff = p->diff ? 1 : 0;
+  c.mask = nullptr;
+  return MMB_OK;
+}
+
+template <typename K> static int opt_in_smem(K kernel, size_t bytes) {
+  if (bytes > 227 * 1024) return MMB_ERR_UNSUPPORTED;
+  if (bytes > 48 * 1024 &&
+      cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess) {
+    set_last_cuda_error(cudaGetLastError());
+    return MMB_ERR_CUDA;
+  }
+  return MMB_OK;
+}
+
+struct ExtractWs { int* counts; int* offsets; size_t bytes; };
+static ExtractWs carve_extract(void* base, int B, int A) {
+  Carver c(base);
+  ExtractWs w;
+  w.counts = c.take<int>((size_t)B * A);
+  w.offsets = c.take<int>((size_t)B * (A + 1));
+  w.bytes = c.off;
+  return w;
+}
+
+template <typename T, bool FUSED, bool WRITE>
+static int launch_peak_rows(const PeakArgs& a, cudaStream_t st) {
+  size_t smem = (size_t)a.R * sizeof(T) + 16;
+  if (FUSED) smem += (size_t)(a.cfar.hi - a.cfar.lo + 1) * sizeof(double);
+  int rc = opt_in_smem(peak_rows_kernel<T, FUSED, WRITE>, smem);
+  if (rc) return rc;
+  peak_rows_kernel<T, FUSED, WRITE><<<a.rows, ROW_THREADS, smem, st>>>(a);
+  return check_launch();
+}
+
+static int fill_peak(const mmb_extract_params* p, const void* src, PeakArgs& a) {
+  if (!p || !src) return MMB_ERR_NULL_POINTER;
+  if (p->B <= 0 || p->A <= 0 || p->R <= 1) return MMB_ERR_INVALID_SHAPE;
+  if (p->dtype != MMB_F32 && p->dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  a.mask = nullptr; a.mask_row_stride = p->R;
+  a.rows = p->B * p->A; a.A = p->A; a.R = p->R;
+  a.res = (float)p->res; a.diff = p->diff ? 1 : 0; a.steep = p->steep_fact;
+  a.counts = nullptr; a.offsets = nullptr; a.ent_val = nullptr; a.ent_row = nullptr; a.cap = 0;
+  if (p->fused) {
+    if (p->cfar.B != p->B || p->cfar.A != p->A || p->cfar.R != p->R || p->cfar.dtype != p->dtype)
+      return MMB_ERR_INVALID_SHAPE;
+    return fill_cfar(&p->cfar, src, a.cfar);
+  }
+  a.mask = src;
+  return MMB_OK;
+}
+
+}  // namespace mmb
+
+using namespace mmb;
+
+extern "C" {
+
+int mmb_sample_weights_fwd(int32_t N, int32_t n, int32_t pt_cols, int32_t H, int32_t W, int32_t dtype,
+                           double cart_res, const void* mask, const void* pts, void* w_out, void* stream) {
+  if (N <= 0 || n <= 0 || H <= 1 || W <= 1 || pt_cols < 2) return MMB_ERR_INVALID_SHAPE;
+  if (dtype != MMB_F32 && dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  if (!mask || !pts || !w_out) return MMB_ERR_NULL_POINTER;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int blocks = (int)(((size_t)N * n + 255) / 256);
+  if (dtype == MMB_F32)
+    sample_weights_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(mask), static_cast<const float*>(pts),
+                                                         pt_cols, N, n, H, W, (float)cart_res, static_cast<float*>(w_out));
+  else
+    sample_weights_kernel<double><<<blocks, 256, 0, st>>>(static_cast<const double*>(mask),
+                                                          static_cast<const double*>(pts), pt_cols, N, n, H, W, cart_res,
+                                                          static_cast<double*>(w_out));
+  return check_launch();
+}
+
+int mmb_sample_weights_bwd(int32_t N, int32_t n, int32_t pt_cols, int32_t H, int32_t W, int32_t dtype,
+                           double cart_res, const void* grad_w, const void* pts, void* grad_mask, void* stream) {
+  if (N <= 0 || n <= 0 || H <= 1 || W <= 1 || pt_cols < 2) return MMB_ERR_INVALID_SHAPE;
+  if (dtype != MMB_F32 && dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  if (!grad_w || !pts || !grad_mask) return MMB_ERR_NULL_POINTER;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int blocks = (int)(((size_t)N * n + 255) / 256);
+  if (dtype == MMB_F32)
+    sample_weights_bwd_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(grad_w),
+                                                             static_cast<const float*>(pts), pt_cols, N, n, H, W,
+                                                             (float)cart_res, static_cast<float*>(grad_mask));
+  else
+    sample_weights_bwd_kernel<double><<<blocks, 256, 0, st>>>(static_cast<const double*>(grad_w),
+                                                              static_cast<const double*>(pts), pt_cols, N, n, H, W,
+                                                              cart_res, static_cast<double*>(grad_mask));
+  return check_launch();
+}
+
+int mmb_polar_to_cart(int32_t B, int32_t A, int32_t R, int32_t width, int32_t dtype, int32_t scan_u8,
+                      const void* scan, const void* azimuths, const void* range_tab, const void* angle_tab,
+                      double radar_res, int32_t interpolate_crossover, int32_t fix_wobble, void* out, void* stream) {
+  if (B <= 0 || A <= 1 || R <= 1 || width <= 0) return MMB_ERR_INVALID_SHAPE;
+  if (dtype != MMB_F32 && dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  if (scan_u8 && dtype != MMB_F32) return MMB_ERR_UNSUPPORTED;
+  if (!scan || !azimuths || !range_tab || !angle_tab || !out) return MMB_ERR_NULL_POINTER;
+  PolarArgs a;
+  a.scan = scan; a.scan_kind = scan_kind_of(dtype, scan_u8);
+  a.scan_row_stride = scan_u8 ? (size_t)R + 11 : (size_t)R; a.scan_batch_stride = 0;
+  a.azimuths = azimuths; a.range_tab = range_tab; a.angle_tab = angle_tab; a.out = out;
+  a.B = B; a.A = A; a.R = R; a.width = width;
+  a.interpolate_crossover = interpolate_crossover ? 1 : 0; a.fix_wobble = fix_wobble ? 1 : 0;
+  a.radar_res = radar_res;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  dim3 grid((width * width + ROW_THREADS - 1) / ROW_THREADS, B);
+  int rc;
+  if (dtype == MMB_F32) {
+    const size_t smem = (size_t)A * sizeof(float);
+    if ((rc = opt_in_smem(polar_to_cart_kernel<float>, smem))) return rc;
+    polar_to_cart_kernel<float><<<grid, ROW_THREADS, smem, st>>>(a);
+  } else {
+    const size_t smem = (size_t)A * sizeof(double);
+    if ((rc = opt_in_smem(polar_to_cart_kernel<double>, smem))) return rc;
+    polar_to_cart_kernel<double><<<grid, ROW_THREADS, smem, st>>>(a);
+  }
+  return check_launch();
+}
+
+int mmb_cfar_columns(const mmb_cfar_params* p, int32_t* w2, int32_t* mincol, int32_t* maxcol) {
+  CfarArgs c;
+  const int rc = fill_cfar(p, nullptr, c);
+  if (rc) return rc;
+  if (w2) *w2 = c.w2;
+  if (mincol) *mincol = c.mincol;
+  if (maxcol) *maxcol = c.maxcol;
+  return MMB_OK;
+}
+
+int mmb_cfar_mask(const mmb_cfar_params* p, const void* scan, void* mask, void* stream) {
+  CfarArgs c;
+  int rc = fill_cfar(p, scan, c);
+  if (rc) return rc;
+  if (!scan || !mask) return MMB_ERR_NULL_POINTER;
+  c.mask = mask;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t smem = (size_t)(c.hi - c.lo + 1) * sizeof(double);
+#define MMB_CFAR_LAUNCH(T, D)                                                  \
+  do {                                                                         \
+    if ((rc = opt_in_smem(cfar_mask_kernel<T, D>, smem))) return rc;           \
+    cfar_mask_kernel<T, D><<<c.rows, ROW_THREADS, smem, st>>>(c);              \
+  } while (0)
+  if (p->dtype == MMB_F32) { if (c.diff) MMB_CFAR_LAUNCH(float, true); else MMB_CFAR_LAUNCH(float, false); }
+  else { if (c.diff) MMB_CFAR_LAUNCH(double, true); else MMB_CFAR_LAUNCH(double, false); }
+#undef MMB_CFAR_LAUNCH
+  return check_launch();
+}
+
+size_t mmb_extract_workspace_bytes(int32_t B, int32_t A) {
+  if (B <= 0 || A <= 0) return 0;
+  return carve_extract(nullptr, B, A).bytes;
+}
+
+int mmb_extract_count(const mmb_extract_params* p, const void* mask_or_scan, void* workspace, size_t workspace_bytes,
+                      int32_t* totals, void* stream) {
+  PeakArgs a;
+  int rc = fill_peak(p, mask_or_scan, a);
+  if (rc) return rc;
+  if (!workspace || !totals) return MMB_ERR_NULL_POINTER;
+  if (reinterpret_cast<uintptr_t>(workspace) % 256) return MMB_ERR_MISALIGNED;
+  ExtractWs w = carve_extract(workspace, p->B, p->A);
+  if (workspace_bytes < w.bytes) return MMB_ERR_WORKSPACE_TOO_SMALL;
+  a.counts = w.counts;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (p->dtype == MMB_F32) rc = p->fused ? launch_peak_rows<float, true, false>(a, st) : launch_peak_rows<float, false, false>(a, st);
+  else rc = p->fused ? launch_peak_rows<double, true, false>(a, st) : launch_peak_rows<double, false, false>(a, st);
+  if (rc) return rc;
+  row_offsets_kernel<<<p->B, 256, 0, st>>>(w.counts, p->A, w.offsets, totals);
+  return check_launch();
+}
+
+int mmb_extract_write(const mmb_extract_params* p, const void* mask_or_scan, const void* azimuths, const void* T_ab,
+                      void* workspace, size_t workspace_bytes, int32_t entry_cap, void* ent_val, int32_t* ent_row,
+                      int32_t out_cap, void* points_out, void* stream) {
+  PeakArgs a;
+  int rc = fill_peak(p, mask_or_scan, a);
+  if (rc) return rc;
+  if (!workspace || !azimuths || !ent_val || !ent_row || !points_out) return MMB_ERR_NULL_POINTER;
+  if (entry_cap <= 0 || out_cap <= 0) return MMB_ERR_INVALID_SHAPE;
+  if (reinterpret_cast<uintptr_t>(workspace) % 256) return MMB_ERR_MISALIGNED;
+  ExtractWs w = carve_extract(workspace, p->B, p->A);
+  if (workspace_bytes < w.bytes) return MMB_ERR_WORKSPACE_TOO_SMALL;
+  a.counts = w.counts; a.offsets = w.offsets; a.ent_val = ent_val; a.ent_row = ent_row; a.cap = entry_cap;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (p->dtype == MMB_F32) rc = p->fused ? launch_peak_rows<float, true, true>(a, st) : launch_peak_rows<float, false, true>(a, st);
+  else rc = p->fused ? launch_peak_rows<double, true, true>(a, st) : launch_peak_rows<double, false, true>(a, st);
+  if (rc) return rc;
+  dim3 grid((out_cap + 255) / 256, p->B);
+  if (p->dtype == MMB_F32)
+    peak_points_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(ent_val), ent_row, w.offsets,
+                                                    static_cast<const float*>(azimuths), static_cast<const float*>(T_ab),
+                                                    p->A, entry_cap, out_cap, static_cast<float*>(points_out));
+  else
+    peak_points_kernel<double><<<grid, 256, 0, st>>>(static_cast<const double*>(ent_val), ent_row, w.offsets,
+                                                     static_cast<const double*>(azimuths),
+                                                     static_cast<const double*>(T_ab), p->A, entry_cap, out_cap,
+                                                     static_cast<double*>(points_out));
+  return check_launch();
+}
+
+// ---- K-strongest ---------------------------------------------------------------------------------
+struct KStrongWs { int* sel_bin; int* counts; int* offsets; size_t bytes; };
+static KStrongWs carve_kstrong(void* base, int B, int A, int k) {
+  Carver c(base);
+  KStrongWs w;
+  w.sel_bin = c.take<int>((size_t)B * A * k);
+  w.counts = c.take<int>((size_t)B * A);
+  w.offsets = c.take<int>((size_t)B * (A + 1));
+  w.bytes = c.off;
+  return w;
+}
+
+static int validate_kstrong(const mmb_kstrong_params* p) {
+  if (!p) return MMB_ERR_NULL_POINTER;
+  if (p->B <= 0 || p->A <= 0 || p->R <= 0 || p->k <= 0 || p->k > 1024) return MMB_ERR_INVALID_SHAPE;
+  if (p->dtype != MMB_F32 && p->dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  if (!(p->res > 0.0)) return MMB_ERR_INVALID_SHAPE;
+  return MMB_OK;
+}
+
+size_t mmb_kstrong_workspace_bytes(const mmb_kstrong_params* p) {
+  if (validate_kstrong(p)) return 0;
+  return carve_kstrong(nullptr, p->B, p->A, p->k).bytes;
+}
+
+int mmb_kstrong_select(const mmb_kstrong_params* p, const void* scan, void* workspace, size_t workspace_bytes,
+                       int32_t* totals, void* stream) {
+  int rc = validate_kstrong(p);
+  if (rc) return rc;
+  if (!scan || !workspace || !totals) return MMB_ERR_NULL_POINTER;
+  if (reinterpret_cast<uintptr_t>(workspace) % 256) return MMB_ERR_MISALIGNED;
+  KStrongWs w = carve_kstrong(workspace, p->B, p->A, p->k);
+  if (workspace_bytes < w.bytes) return MMB_ERR_WORKSPACE_TOO_SMALL;
+  // detector.inl:45-51: `res` is a float there, the column bounds are doubles
+  const double resf = (double)(float)p->res;
+  double mincol = p->minr / resf;
+  if (mincol > p->R || mincol < 0) mincol = 0;
+  double maxcol = p->maxr / resf;
+  if (maxcol > p->R || maxcol < 0) maxcol = p->R;
+  KStrongArgs a;
+  a.scan = scan;
+  a.scan_kind = p->scan_u8 ? IN_U8 : IN_F32;
+  a.scan_row_stride = p->scan_u8 ? (size_t)p->R + 11 : (size_t)p->R;
+  a.rows = p->B * p->A; a.A = p->A; a.R = p->R; a.k = p->k;
+  a.j0 = (int)mincol;
+  int j1 = (int)maxcol;
+  if ((double)j1 < maxcol) j1 += 1;                  // `j < maxcol` with a double bound
+  if (j1 > p->R) j1 = p->R;
+  a.j1 = j1 < a.j0 ? a.j0 : j1;
+  a.N = maxcol - mincol; a.t2 = p->threshold2; a.t3 = p->threshold3;
+  a.sel_bin = w.sel_bin; a.counts = w.counts;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t smem = (size_t)(a.j1 - a.j0 + 1) * sizeof(float);
+  if ((rc = opt_in_smem(kstrong_rows_kernel, smem))) return rc;
+  kstrong_rows_kernel<<<a.rows, ROW_THREADS, smem, st>>>(a);
+  if ((rc = check_launch())) return rc;
+  row_offsets_kernel<<<p->B, 256, 0, st>>>(w.counts, p->A, w.offsets, totals);
+  return check_launch();
+}
+
+int mmb_kstrong_write(const mmb_kstrong_params* p, const void* azimuths, void* workspace, size_t workspace_bytes,
+                      int32_t out_cap, void* points_out, int32_t* rows_out, int32_t* bins_out, void* stream) {
+  int rc = validate_kstrong(p);
+  if (rc) return rc;
+  if (!azimuths || !workspace || !points_out) return MMB_ERR_NULL_POINTER;
+  if (out_cap <= 0) return MMB_ERR_INVALID_SHAPE;
+  KStrongWs w = carve_kstrong(workspace, p->B, p->A, p->k);
+  if (workspace_bytes < w.bytes) return MMB_ERR_WORKSPACE_TOO_SMALL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  dim3 grid((p->A * p->k + 255) / 256, p->B);
+  if (p->dtype == MMB_F32)
+    kstrong_points_kernel<float><<<grid, 256, 0, st>>>(w.sel_bin, w.counts, w.offsets, static_cast<const float*>(azimuths),
+                                                       p->A, p->k, (float)p->res, p->range_offset, out_cap,
+                                                       static_cast<float*>(points_out), rows_out, bins_out);
+  else
+    kstrong_points_kernel<double><<<grid, 256, 0, st>>>(w.sel_bin, w.counts, w.offsets,
+                                                        static_cast<const double*>(azimuths), p->A, p->k, (float)p->res,
+                                                        p->range_offset, out_cap, static_cast<double*>(points_out),
+                                                        rows_out, bins_out);
+  return check_launch();
+}
+
+}  // extern "C"

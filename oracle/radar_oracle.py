@@ -254,17 +254,22 @@ def polar_to_cartesian(fft: np.ndarray, azimuths: np.ndarray, radar_resolution: 
 def kstrongest(fft: np.ndarray, azimuths: np.ndarray, res: float, kstrong=12, threshold2=0.0, threshold3=0.216,
                minr=2.0, maxr=80.0, range_offset=-0.31):
     """`detector.inl:39-85` with the ordering fixed as SURVEY.md section 8a note: per azimuth,
-    mean over the bins j = ceil(minr/res) .. (while j < maxr/res), divided by N = maxr/res - minr/res
+    mean over the bins j = int(minr/res) .. (while j < maxr/res), divided by N = maxr/res - minr/res
     (a double, not the bin count, `:47-61`); keep bins with value >= mean*threshold2 + threshold3;
     take up to k by descending intensity, ties to the lower bin; rho = j*res + range_offset;
     (x, y) = (rho cos phi, rho sin phi) (`navtech_extraction_module.cpp:33-39`).
     Returns per scan (points (P,3) float32, rows int32, bins int32), azimuth-major, selection order.
     """
     B, A, R = fft.shape
-    mincol = minr / res
-    maxcol = min(maxr / res, float(R))
+    resf = float(np.float32(res))                      # `const float& res`; minr_/res is evaluated in double
+    mincol = minr / resf
+    if mincol > R or mincol < 0:
+        mincol = 0.0
+    maxcol = maxr / resf
+    if maxcol > R or maxcol < 0:
+        maxcol = float(R)
     N = maxcol - mincol
-    j0 = int(np.ceil(mincol))
+    j0 = int(mincol)                                   # `for (int j = mincol; j < maxcol; ++j)`
     js = np.arange(j0, R)
     js = js[js < maxcol]
     out = []
@@ -280,7 +285,7 @@ def kstrongest(fft: np.ndarray, azimuths: np.ndarray, res: float, kstrong=12, th
             vals = fft[b, a, cand]
             order = np.lexsort((cand, -vals.astype(np.float64)))[:kstrong]
             for j in cand[order]:
-                rho = np.float32(j * res + range_offset)
+                rho = np.float32(float(np.float32(j) * np.float32(res)) + range_offset)
                 phi = np.float32(azimuths[b, a])
                 pts.append((rho * np.cos(phi), rho * np.sin(phi), 0.0))
                 rows.append(a); bins.append(j)
