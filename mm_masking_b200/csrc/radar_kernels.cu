@@ -147,9 +147,14 @@ __global__ void __launch_bounds__(ROW_THREADS) polar_to_cart_kernel(PolarArgs a)
   for (int i = threadIdx.x; i < a.A; i += blockDim.x) saz[i] = az[i];
   __syncthreads();
 
+  // 16 x 16 pixel tile per block (a warp covers 16 x 2 pixels): neighbouring pixels sample
+  // neighbouring polar bins, so a compact tile touches few 32-byte sectors of the scan
   const int npix = a.width * a.width;
-  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
-  if (pix >= npix) return;
+  const int tiles_x = (a.width + 15) >> 4;
+  const int px = (blockIdx.x % tiles_x) * 16 + (threadIdx.x & 15);
+  const int py = (blockIdx.x / tiles_x) * 16 + (threadIdx.x >> 4);
+  if (px >= a.width || py >= a.width) return;
+  const int pix = py * a.width + px;
   const T range = static_cast<const T*>(a.range_tab)[pix];
   const T angle = static_cast<const T*>(a.angle_tab)[pix];
   const T res = (T)a.radar_res, half = (T)(a.radar_res / 2);
@@ -326,7 +331,8 @@ __device__ __forceinline__ void stage_arr(const PeakArgs& a, size_t row, T* arr,
   if (FUSED) {
     Scan<T> sc; sc.base = a.cfar.scan; sc.kind = a.cfar.scan_kind; sc.row_stride = a.cfar.scan_row_stride;
     stage_prefix<T>(sc, row, a.cfar.lo, a.cfar.hi, pre, wt);
-    for (int k = threadIdx.x; k < a.R; k += blockDim.x) {
+    const int k0 = max(a.cfar.mincol - 1, 0), k1 = min(a.cfar.maxcol + 1, a.R);   // arr is read on [mincol-1, maxcol]
+    for (int k = k0 + threadIdx.x; k < k1; k += blockDim.x) {
       T m = (T)0;
       if (k >= a.cfar.mincol && k < a.cfar.maxcol) {
         m = cfar_mask_value<T>(a.cfar, sc.at(row, k), cfar_threshold_at(a.cfar, pre, k));
@@ -365,9 +371,11 @@ __global__ void __launch_bounds__(ROW_THREADS) peak_rows_kernel(PeakArgs a) {
   const size_t row = blockIdx.x;
   stage_arr<T, FUSED>(a, row, arr, pre, wt);
 
-  // each thread owns a contiguous chunk so that ordinals follow the range order
-  const int chunk = (a.R + blockDim.x - 1) / blockDim.x;
-  const int s = threadIdx.x * chunk, e = min(s + chunk, a.R);
+  // each thread owns a contiguous chunk so that ordinals follow the range order; with the fused
+  // source the mask is zero outside [mincol, maxcol), so entries can only sit in [mincol-1, maxcol)
+  const int c0 = FUSED ? max(a.cfar.mincol - 1, 0) : 0, c1 = FUSED ? min(a.cfar.maxcol, a.R) : a.R;
+  const int chunk = (c1 - c0 + blockDim.x - 1) / blockDim.x;
+  const int s = c0 + threadIdx.x * chunk, e = min(s + chunk, c1);
   int cnt = 0;
   for (int k = s; k < e; ++k) cnt += peak_value<T>(a, arr, k) != (T)0 ? 1 : 0;
   int total;
@@ -678,7 +686,8 @@ int mmb_polar_to_cart(int32_t B, int32_t A, int32_t R, int32_t width, int32_t dt
   a.interpolate_crossover = interpolate_crossover ? 1 : 0; a.fix_wobble = fix_wobble ? 1 : 0;
   a.radar_res = radar_res;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  dim3 grid((width * width + ROW_THREADS - 1) / ROW_THREADS, B);
+  const int tiles = (width + 15) / 16;
+  dim3 grid(tiles * tiles, B);
   int rc;
   if (dtype == MMB_F32) {
     const size_t smem = (size_t)A * sizeof(float);
