@@ -158,7 +158,7 @@ def run_ours(args, wl, rank, world, local_rank):
     import numpy as np
     import torch
     import torch.distributed as dist
-    from mm_masking_b200 import _capi
+    from mm_masking_b200 import _capi, dist as mdist
     from mm_masking_b200.dICP import ICP
     from mm_masking_b200.dICP.ICP import _IcpFunction  # noqa: F401  (same code path as ICP.icp)
 
@@ -217,11 +217,7 @@ def run_ours(args, wl, rank, world, local_rank):
             b.record()
         barrier()
         t1 = time.time()
-        ms = sum(a.elapsed_time(b) for a, b in ev)
-        if world > 1:
-            t = torch.tensor([ms], dtype=torch.float64, device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
+        ms = mdist.max_over_ranks(sum(a.elapsed_time(b) for a, b in ev), device=dev)
         return ms / steps, t0, t1
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
