@@ -48,6 +48,7 @@ WORKLOADS = {
 }
 METRIC = "icp_pairs_per_sec_fwd_bwd"
 UNIT = "pairs/s"
+NN_BACKENDS = {"auto": 0, "brute": 1, "grid": 2}
 FLOP_PER_PAIR = 8          # 3 sub, 3 mul, 2 add: the distance `torch.cdist` evaluates
 
 
@@ -180,6 +181,7 @@ def run_ours(args, wl, rank, world, local_rank):
     alg = ICP(icp_type="pt2pl", differentiable=True, max_iterations=K, tolerance=1e-5)
     alg.const_iter = True
     alg.nn_slices = args.nn_slices
+    alg.nn_backend = NN_BACKENDS[args.nn_backend]
     call = dict(trim_dist=5.0, loss_fn={"name": "cauchy", "metric": 1.0}, dim=wl["dim"])
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
 
@@ -244,6 +246,7 @@ def run_ours(args, wl, rank, world, local_rank):
     p.loss_kind, p.loss_metric, p.has_weight, p.save_for_backward = _capi.LOSS_CAUCHY, 1.0, 1, 1
     p.tolerance, p.tanh_steepness, p.match_ratio_thresh = 1e-5, 5.0, 0.1
     p.nn_slices = args.nn_slices
+    p.nn_backend = NN_BACKENDS[args.nn_backend]
     ws_bytes, sv_bytes = lib.mmb_icp_workspace_bytes(p), lib.mmb_icp_saved_bytes(p)
     f32 = dict(dtype=torch.float32, device=dev)
     bufs = dict(ws=torch.empty(ws_bytes, dtype=torch.uint8, device=dev), sv=torch.empty(sv_bytes, dtype=torch.uint8, device=dev),
@@ -251,8 +254,9 @@ def run_ours(args, wl, rank, world, local_rank):
                 wh=torch.zeros((N, K, n), **f32), co=torch.zeros((N, K), **f32),
                 cv=torch.zeros(N, dtype=torch.uint8, device=dev), it=torch.zeros(N, **f32), mr=torch.zeros(N, **f32),
                 idn=torch.zeros(1, dtype=torch.int32, device=dev))
-    ms3, cnt3 = (C.c_float * 4)(), (C.c_int32 * 4)()
-    acc_ms, acc_n = [0.0] * 4, [0] * 4
+    NC = _capi.PROFILE_CLASSES
+    ms3, cnt3 = (C.c_float * NC)(), (C.c_int32 * NC)()
+    acc_ms, acc_n = [0.0] * NC, [0] * NC
     w_det = d_w.detach()
     for rep in range(2 + min(args.steps, 5)):
         flush.fill_(1)
@@ -264,7 +268,7 @@ def run_ours(args, wl, rank, world, local_rank):
                                           ms3, cnt3)
         _capi.check(rc, "mmb_icp_forward_profiled")
         if rep >= 2:
-            for c in range(4):
+            for c in range(NC):
                 acc_ms[c] += ms3[c]; acc_n[c] += cnt3[c]
     nn_ms = acc_ms[0] / max(acc_n[0], 1)            # average duration of one NN launch
     step_ms = acc_ms[1] / max(acc_n[1], 1)
@@ -323,7 +327,8 @@ def run_ours(args, wl, rank, world, local_rank):
                                     "MEASURED_PEAKS.json has no CUDA-core FP32 entry",
                      "peak_detail": peak, "share_of_forward": acc_ms[0] / max(sum(acc_ms), 1e-9),
                      "forward_ms": fwd_ms, "step_kernel_ms_per_launch": step_ms,
-                     "bound_pass_ms": acc_ms[3] / reps,
+                     "bound_pass_ms": acc_ms[3] / reps, "grid_build_ms": acc_ms[4] / reps,
+                     "nn_backend": args.nn_backend,
                      "hbm_gbs_measured_peak": hbm_peak},
         "cpu_baseline": cpu,
         "clocks": clocks,
@@ -342,6 +347,8 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--ref-pairs", type=int, default=2, help="pairs per CPU-reference step (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--nn-backend", default="auto", choices=sorted(NN_BACKENDS),
+                    help="nearest-neighbour backend: exact cell grid (auto for m >= 8192) or brute force; same indices")
     ap.add_argument("--nn-slices", type=int, default=0, help="tuning: target slices per query tile (0 = library default)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]

@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define MMB_ABI_VERSION 1
+#define MMB_ABI_VERSION 2
 
 typedef enum mmb_status {
   MMB_OK = 0,
@@ -36,6 +36,11 @@ typedef enum mmb_status {
 enum { MMB_F32 = 0, MMB_F64 = 1 };
 enum { MMB_PT2PL = 0, MMB_PT2PT = 1 };
 enum { MMB_LOSS_NONE = 0, MMB_LOSS_HUBER = 1, MMB_LOSS_CAUCHY = 2 };
+/* Nearest-neighbour backend.  Both return the same indices (exact squared differences, lowest
+ * index on ties); BRUTE evaluates all n*m pairs like nn.py:32, GRID visits only the cells that can
+ * hold the neighbour.  AUTO: GRID when m >= 8192. */
+enum { MMB_NN_AUTO = 0, MMB_NN_BRUTE = 1, MMB_NN_GRID = 2 };
+#define MMB_PROFILE_CLASSES 8
 
 int mmb_abi_version(void);
 const char* mmb_status_string(int status);
@@ -63,7 +68,7 @@ typedef struct mmb_icp_params {
   int32_t has_weight;      /* prior per-point weights given (ICP.py:310-316) */
   int32_t save_for_backward;
   int32_t nn_slices;       /* 0 = choose automatically; else target slices per query tile */
-  int32_t reserved;
+  int32_t nn_backend;      /* MMB_NN_* */
   double tolerance;        /* ICP.py:30 */
   double trim_dist;
   double loss_metric;
@@ -92,10 +97,11 @@ int mmb_icp_forward(const mmb_icp_params* p, const void* source, const void* tar
 /*
  * mmb_icp_forward plus per-kernel-class device timing, for bench.py's roofline figures.  CUDA
  * events are recorded on `stream` around every launch; the call synchronises on the last one
- * and writes to HOST memory: host_ms[0..3] = summed durations (ms) of the nearest-neighbour
- * launches, the step (residual/normal-equation/solve) launches, the rest (init, target
- * packing, result assembly) and the cold-start bound pass (subsample pack + search);
- * host_launches[0..3] = number of timed intervals in each class.
+ * and writes to HOST memory, MMB_PROFILE_CLASSES entries each: host_ms[c] = summed durations (ms)
+ * of class c = 0 nearest-neighbour launches, 1 step (residual/normal-equation/solve) launches,
+ * 2 the rest (init, target packing, result assembly), 3 the cold-start bound pass (subsample pack +
+ * search, brute-force backend), 4 the cell-grid build (grid backend); host_launches[c] = number
+ * of timed intervals in class c.
  */
 int mmb_icp_forward_profiled(const mmb_icp_params* p, const void* source, const void* target,
                              const void* T_init, const void* weight, void* T_out, void* pc_out,
@@ -118,15 +124,17 @@ int mmb_icp_backward(const mmb_icp_params* p, const void* source, const void* ta
                      size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------------
- * Brute-force 1-NN.  Replaces external/dICP/dICP/nn.py:23-40 / :72-92
+ * Exact 1-NN (brute force or cell grid, MMB_NN_*).  Replaces external/dICP/dICP/nn.py:23-40 / :72-92
  * (`torch.cdist` -> `argmin` -> `gather`): index of the nearest target row for every query
  * row, squared differences evaluated exactly, lowest index on ties.  dim == 2 ignores z.
  *   query (N,n,3)  target (N,m,target_cols)  idx_out (N,n) int32
  * ---------------------------------------------------------------------------------------- */
-size_t mmb_nn_workspace_bytes(int32_t N, int32_t n, int32_t m, int32_t nn_slices);
+size_t mmb_nn_workspace_bytes(int32_t N, int32_t n, int32_t m, int32_t dtype, int32_t nn_slices,
+                              int32_t nn_backend);
 int mmb_nn_search(int32_t N, int32_t n, int32_t m, int32_t target_cols, int32_t dtype,
-                  int32_t dim, int32_t nn_slices, const void* query, const void* target,
-                  int32_t* idx_out, void* workspace, size_t workspace_bytes, void* stream);
+                  int32_t dim, int32_t nn_slices, int32_t nn_backend, const void* query,
+                  const void* target, int32_t* idx_out, void* workspace, size_t workspace_bytes,
+                  void* stream);
 
 
 /* ------------------------------------------------------------------------------------------

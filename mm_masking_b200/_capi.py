@@ -15,6 +15,8 @@ LIB_PATH = os.path.join(_HERE, "libmm_masking_b200.so")
 F32, F64 = 0, 1
 PT2PL, PT2PT = 0, 1
 LOSS_NONE, LOSS_HUBER, LOSS_CAUCHY = 0, 1, 2
+NN_AUTO, NN_BRUTE, NN_GRID = 0, 1, 2
+PROFILE_CLASSES = 8
 
 
 class IcpParams(C.Structure):
@@ -24,7 +26,7 @@ class IcpParams(C.Structure):
         ("dtype", C.c_int32), ("icp_type", C.c_int32), ("dim", C.c_int32), ("max_iterations", C.c_int32),
         ("differentiable", C.c_int32), ("const_iter", C.c_int32), ("use_trim", C.c_int32),
         ("loss_kind", C.c_int32), ("has_weight", C.c_int32), ("save_for_backward", C.c_int32),
-        ("nn_slices", C.c_int32), ("reserved", C.c_int32),
+        ("nn_slices", C.c_int32), ("nn_backend", C.c_int32),
         ("tolerance", C.c_double), ("trim_dist", C.c_double), ("loss_metric", C.c_double),
         ("tanh_steepness", C.c_double), ("match_ratio_thresh", C.c_double),
     ]
@@ -63,8 +65,8 @@ SIGNATURES = {
     "mmb_icp_forward_profiled": (C.c_int, [C.POINTER(IcpParams)] + [_P] * 15 + [C.c_size_t, _P,
                                                                                  C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
     "mmb_icp_backward": (C.c_int, [C.POINTER(IcpParams)] + [_P] * 11 + [C.c_size_t, _P]),
-    "mmb_nn_workspace_bytes": (C.c_size_t, [C.c_int32] * 4),
-    "mmb_nn_search": (C.c_int, [C.c_int32] * 7 + [_P] * 4 + [C.c_size_t, _P]),
+    "mmb_nn_workspace_bytes": (C.c_size_t, [C.c_int32] * 6),
+    "mmb_nn_search": (C.c_int, [C.c_int32] * 8 + [_P] * 4 + [C.c_size_t, _P]),
     "mmb_sample_weights_fwd": (C.c_int, [C.c_int32] * 6 + [C.c_double, _P, _P, _P, _P]),
     "mmb_sample_weights_bwd": (C.c_int, [C.c_int32] * 6 + [C.c_double, _P, _P, _P, _P]),
     "mmb_polar_to_cart": (C.c_int, [C.c_int32] * 6 + [_P] * 4 + [C.c_double, C.c_int32, C.c_int32, _P, _P]),
@@ -101,7 +103,7 @@ def load_library(path: str | None = None):
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)
         fn.restype, fn.argtypes = res, args
-    if lib.mmb_abi_version() != 1:
+    if lib.mmb_abi_version() != 2:
         raise MmbError("libmm_masking_b200.so ABI version mismatch")
     _lib = lib
     return lib

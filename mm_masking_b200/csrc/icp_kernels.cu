@@ -37,11 +37,26 @@ constexpr float PAD_COORD = __builtin_huge_valf();   // filter copy padding: nev
 constexpr int NN_SUB_STRIDE = 8;       // cold start: bound pass over every 8th target (DESIGN.md "cold start")
 constexpr int NN_SUB_MIN_M = 8192;     // below this the bound pass is not worth a launch
 
+// Exact cell-grid search (second NN backend): G x G cells over the scan's footprint, targets sorted
+// by the Morton code of their (clamped) cell so that every cell of every coarser level is one
+// contiguous range of the sorted copy.
+constexpr int GRID_BITS = 8;
+constexpr int GRID_G = 1 << GRID_BITS;          // cells per axis at the finest level
+constexpr int GRID_CELLS = GRID_G * GRID_G;
+constexpr int GRID_MIN_M = 8192;                // below this the brute-force kernel is used (auto mode)
+constexpr double GRID_MARGIN = 4.0;             // metres added around the scan footprint ...
+constexpr double GRID_MARGIN_REL = 0.125;       // ... plus this fraction of its extent, on every side
+constexpr int GRID_OUTSIDE = GRID_CELLS;        // key of the targets that lie outside the grid
+constexpr int GRIDNN_THREADS = 256;
+constexpr int GRID_STRIDE = GRID_CELLS + 8;     // ints per pair in the start / cursor tables (16-byte aligned rows)
+
 struct IcpPlan {
   int N, n, m, mp, R;            // mp: m rounded up to NN_TILE; R residual rows
   int qtiles, S, tiles_per_slice;
   int D;                         // solved DoF
   int sub_stride, msub, msp, S_sub, sub_tiles_per_slice;   // strided subsample (0 = no bound pass)
+  int grid;                      // 1: cell-grid search, 0: brute force
+  int f64;                       // element type of the sorted copy
 };
 
 // Target slices per query tile.  Measured on B200 (profiles/r01_nn_slices_sweep.md): short blocks
@@ -59,9 +74,11 @@ static int pick_slices(int N, int qtiles, int tiles, int requested) {
   return (int)S;
 }
 
-static IcpPlan make_plan(int N, int n, int m, int icp_type, int dim, int nn_slices) {
+static IcpPlan make_plan(int N, int n, int m, int icp_type, int dim, int nn_slices, int nn_backend, int dtype) {
   IcpPlan pl;
   pl.N = N; pl.n = n; pl.m = m;
+  pl.f64 = dtype == MMB_F64 ? 1 : 0;
+  pl.grid = nn_backend == MMB_NN_GRID || (nn_backend == MMB_NN_AUTO && m >= GRID_MIN_M) ? 1 : 0;
   pl.mp = (int)align_up((size_t)m, NN_TILE);
   pl.R = icp_type == MMB_PT2PT ? 3 * n : n;
   pl.qtiles = (n + NN_QB - 1) / NN_QB;
@@ -71,7 +88,9 @@ static IcpPlan make_plan(int N, int n, int m, int icp_type, int dim, int nn_slic
   pl.S = (tiles + pl.tiles_per_slice - 1) / pl.tiles_per_slice;
   pl.D = dim == 2 ? 3 : 6;
   pl.sub_stride = 0; pl.msub = 0; pl.msp = 0; pl.S_sub = 0; pl.sub_tiles_per_slice = 0;
-  if (m >= NN_SUB_MIN_M) {
+  if (pl.grid) {
+    pl.S = 1; pl.tiles_per_slice = tiles;
+  } else if (m >= NN_SUB_MIN_M) {
     pl.sub_stride = NN_SUB_STRIDE;
     pl.msub = (m + NN_SUB_STRIDE - 1) / NN_SUB_STRIDE;
     pl.msp = (int)align_up((size_t)pl.msub, NN_TILE);
@@ -101,13 +120,19 @@ struct IcpWorkspace {
   int* n_matched;                // (N) rows with w > thresh in the latest iteration
   int* n_start;                  // (N) rows with prior weight > thresh
   int* counters;                 // [0] samples frozen, [1] done flag, [2] iterations executed
+  // cell-grid backend
+  double* geom;                  // (N,4) origin x, y, 1/cell, cell
+  int* cell_start;               // (N, GRID_CELLS+2) first sorted slot of every Morton cell, of the outside bucket, m
+  int* cell_cursor;              // (N, GRID_CELLS+1) counts, then scatter cursors
+  int* keys;                     // (N,m) Morton cell of every target (GRID_OUTSIDE: not in the grid)
+  void* sorted;                  // (N,m) targets in cell order: float4 / 4 doubles (x, y, z, original index)
   size_t bytes;
 };
 
 static IcpWorkspace carve_workspace(void* base, const IcpPlan& pl) {
   Carver c(base);
   IcpWorkspace w;
-  const size_t Nmp = (size_t)pl.N * pl.mp, Nn = (size_t)pl.N * pl.n;
+  const size_t Nmp = pl.grid ? 0 : (size_t)pl.N * pl.mp, Nn = (size_t)pl.N * pl.n;
   w.tx = c.take<float>(Nmp); w.ty = c.take<float>(Nmp); w.tz = c.take<float>(Nmp); w.tn = c.take<float>(Nmp);
   const size_t Nms = (size_t)pl.N * pl.msp;
   w.sx = c.take<float>(Nms); w.sy = c.take<float>(Nms); w.sz = c.take<float>(Nms); w.sn = c.take<float>(Nms);
@@ -124,6 +149,12 @@ static IcpWorkspace carve_workspace(void* base, const IcpPlan& pl) {
   w.n_matched = c.take<int>(pl.N);
   w.n_start = c.take<int>(pl.N);
   w.counters = c.take<int>(8);
+  const size_t Nm = pl.grid ? (size_t)pl.N * pl.m : 0, NG = pl.grid ? (size_t)pl.N : 0;
+  w.geom = c.take<double>(NG * 4);
+  w.cell_start = c.take<int>(NG * GRID_STRIDE);
+  w.cell_cursor = c.take<int>(NG * GRID_STRIDE);
+  w.keys = c.take<int>(Nm);
+  w.sorted = pl.f64 ? static_cast<void*>(c.take<double>(Nm * 4)) : static_cast<void*>(c.take<float>(Nm * 4));
   w.bytes = c.off;
   return w;
 }
@@ -497,6 +528,277 @@ __global__ void merge_only_kernel(const double* pd2, const int* pidx, int S, int
   const size_t total = (size_t)N * n;
   const size_t o = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (o < total) idx_out[o] = merge_partials(pd2, pidx, S, total, o);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3b: exact nearest neighbour on a cell grid (same answer as the brute-force kernel)
+// ---------------------------------------------------------------------------------------------
+// Geometry per pair: a square of GRID_G x GRID_G cells over the footprint of the scan at T_init
+// (+ GRID_MARGIN + GRID_MARGIN_REL of its extent).  Targets inside the square are sorted by the
+// Morton code of their cell, so cell (x,y) of level L (cell size c 2^L) is the contiguous key
+// range [morton(x,y) << 2L, (morton(x,y)+1) << 2L) of the sorted copy and only the finest-level
+// start table is stored.  Targets outside the square (pad rows, distant parts of the map) go to
+// one extra bucket after the last cell; it is scanned only by a query whose best distance reaches
+// the border of the square.  Nothing is ever dropped.
+__host__ __device__ __forceinline__ unsigned morton_spread8(unsigned v) {
+  v = (v | (v << 4)) & 0x0F0Fu;
+  v = (v | (v << 2)) & 0x3333u;
+  v = (v | (v << 1)) & 0x5555u;
+  return v;
+}
+__host__ __device__ __forceinline__ unsigned morton2(unsigned x, unsigned y) {
+  return morton_spread8(x) | (morton_spread8(y) << 1);
+}
+// Morton key of a point given its cell coordinates (doubles), or GRID_OUTSIDE
+__device__ __forceinline__ int grid_key(double fx, double fy) {
+  if (!(fx >= 0.0 && fx < (double)GRID_G && fy >= 0.0 && fy < (double)GRID_G)) return GRID_OUTSIDE;
+  return (int)morton2((unsigned)(int)fx, (unsigned)(int)fy);
+}
+
+// footprint of the transformed scan -> grid origin and cell size.  One block per pair.
+template <typename T, int DIM>
+__global__ void grid_geom_kernel(const T* __restrict__ source, const double* __restrict__ pose, int n,
+                                 double* __restrict__ geom) {
+  const int b = blockIdx.x, tid = threadIdx.x;
+  __shared__ double sP[12];
+  __shared__ double red[4][32];
+  if (tid < 12) sP[tid] = pose[(size_t)b * 12 + tid];
+  __syncthreads();
+  const T* src = source + (size_t)b * n * 3;
+  double lox = 1e300, loy = 1e300, hix = -1e300, hiy = -1e300;
+  for (int i = tid; i < n; i += blockDim.x) {
+    double qx, qy, qz;
+    transform_query<T, DIM>(src + (size_t)i * 3, sP, qx, qy, qz);
+    if (fabs(qx) < 1e30 && fabs(qy) < 1e30) {
+      lox = fmin(lox, qx); hix = fmax(hix, qx); loy = fmin(loy, qy); hiy = fmax(hiy, qy);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    lox = fmin(lox, __shfl_xor_sync(0xffffffffu, lox, o)); loy = fmin(loy, __shfl_xor_sync(0xffffffffu, loy, o));
+    hix = fmax(hix, __shfl_xor_sync(0xffffffffu, hix, o)); hiy = fmax(hiy, __shfl_xor_sync(0xffffffffu, hiy, o));
+  }
+  const int lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  if (lane == 0) { red[0][warp] = lox; red[1][warp] = loy; red[2][warp] = hix; red[3][warp] = hiy; }
+  __syncthreads();
+  if (tid == 0) {
+    for (int w = 1; w < nwarp; ++w) {
+      lox = fmin(lox, red[0][w]); loy = fmin(loy, red[1][w]); hix = fmax(hix, red[2][w]); hiy = fmax(hiy, red[3][w]);
+    }
+    if (!(hix >= lox) || !(hiy >= loy)) { lox = loy = hix = hiy = 0.0; }
+    double ext = fmax(hix - lox, hiy - loy) * (1.0 + 2.0 * GRID_MARGIN_REL) + 2.0 * GRID_MARGIN;
+    if (!(ext < 1e12)) ext = 1e12;
+    const double c = ext / (double)GRID_G;
+    double* g = geom + (size_t)b * 4;
+    g[0] = 0.5 * (lox + hix) - 0.5 * ext; g[1] = 0.5 * (loy + hiy) - 0.5 * ext; g[2] = 1.0 / c; g[3] = c;
+  }
+}
+
+template <typename T>
+__global__ void grid_count_kernel(const T* __restrict__ target, int cols, int N, int m, const double* __restrict__ geom,
+                                  int* __restrict__ keys, int* __restrict__ counts) {
+  const size_t total = (size_t)N * m;
+  for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(g / m);
+    const T* row = target + g * cols;
+    const double* gm = geom + (size_t)b * 4;
+    const int key = grid_key(((double)row[0] - gm[0]) * gm[2], ((double)row[1] - gm[1]) * gm[2]);
+    keys[g] = key;
+    atomicAdd(&counts[(size_t)b * GRID_STRIDE + key], 1);
+  }
+}
+
+// exclusive scan of one pair's GRID_CELLS + 1 counts; the counts array becomes the scatter cursor
+__global__ void __launch_bounds__(1024) grid_scan_kernel(int* __restrict__ counts, int* __restrict__ start) {
+  constexpr int PER = GRID_CELLS / 1024;
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int* cnt = counts + (size_t)b * GRID_STRIDE;
+  int* st = start + (size_t)b * GRID_STRIDE;
+  __shared__ int wsum[32];
+  int v[PER], sum = 0;
+#pragma unroll
+  for (int k = 0; k < PER; k += 4) {
+    const int4 q = *reinterpret_cast<const int4*>(cnt + tid * PER + k);
+    v[k] = q.x; v[k + 1] = q.y; v[k + 2] = q.z; v[k + 3] = q.w;
+    sum += q.x + q.y + q.z + q.w;
+  }
+  int inc = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+  if (lane == 31) wsum[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    int w = wsum[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += t; }
+    wsum[lane] = w;
+  }
+  __syncthreads();
+  int run = inc - sum + (warp > 0 ? wsum[warp - 1] : 0);
+#pragma unroll
+  for (int k = 0; k < PER; ++k) { const int c = v[k]; st[tid * PER + k] = run; cnt[tid * PER + k] = run; run += c; }
+  if (tid == 1023) {
+    const int outside = cnt[GRID_OUTSIDE];
+    st[GRID_OUTSIDE] = run; cnt[GRID_OUTSIDE] = run; st[GRID_OUTSIDE + 1] = run + outside;
+  }
+}
+
+template <typename T> struct SortedPoint;
+template <> struct alignas(16) SortedPoint<float> { float x, y, z; int j; };
+template <> struct alignas(32) SortedPoint<double> { double x, y, z; long long j; };
+
+template <typename T>
+__global__ void grid_scatter_kernel(const T* __restrict__ target, int cols, int N, int m,
+                                    const int* __restrict__ keys, int* __restrict__ cursor,
+                                    SortedPoint<T>* __restrict__ sorted) {
+  const size_t total = (size_t)N * m;
+  for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(g / m), j = (int)(g % m);
+    const T* row = target + g * cols;
+    const int pos = atomicAdd(&cursor[(size_t)b * GRID_STRIDE + keys[g]], 1);
+    SortedPoint<T> sp; sp.x = row[0]; sp.y = row[1]; sp.z = row[2]; sp.j = j;
+    sorted[(size_t)b * m + pos] = sp;
+  }
+}
+
+__device__ __forceinline__ void load_sorted(const SortedPoint<float>* p, double& x, double& y, double& z, int& j) {
+  const float4 v = __ldg(reinterpret_cast<const float4*>(p));
+  x = (double)v.x; y = (double)v.y; z = (double)v.z; j = __float_as_int(v.w);
+}
+__device__ __forceinline__ void load_sorted(const SortedPoint<double>* p, double& x, double& y, double& z, int& j) {
+  const double2 a = __ldg(reinterpret_cast<const double2*>(p)), c = __ldg(reinterpret_cast<const double2*>(p) + 1);
+  x = a.x; y = a.y; z = c.x; j = (int)__double_as_longlong(c.y);
+}
+
+struct GridNNArgs {
+  const void* source; const void* target; const double* pose;
+  const double* geom; const int* cell_start; const void* sorted;
+  const int* idx_prev; const int* frozen; const int* counters;
+  double* pd2; int* pidx;
+  int N, n, m, cols;
+};
+
+// One WARP per query; the 32 lanes share the candidates of a cell range (coalesced 16-byte loads
+// of the sorted copy), so there is no divergence and no per-thread tail.  Every candidate is
+// compared exactly -- fp64 squared differences on the caller's own coordinates (the sorted copy
+// holds them unrounded), ties to the lowest ORIGINAL index -- so the result is the brute-force
+// result whatever the order inside a cell.
+//   square scan: with an upper bound D on the nearest distance, every target that can win or tie
+//     lies in the square [q - D, q + D]^2; it is scanned at the finest level where it spans at most
+//     3 x 3 cells (plus the outside bucket when it pokes out of the grid).
+//   warm start (iterations >= 1): D = exact distance to the previous iteration's neighbour at the
+//     new pose -> one square scan.
+//   cold start: 3 x 3 blocks around the query's cell at level 0, 1, 2, ... until a block holds a
+//     target; that gives D for the square scan (skipped when D is already below the block's cell
+//     size and below the distance to the grid border: nothing outside the block can win or tie).
+constexpr int GRIDNN_WARPS = GRIDNN_THREADS / 32;
+
+__device__ __forceinline__ int clamp_cell(double v) {
+  if (!(v >= 0.0)) return 0;
+  if (v >= (double)GRID_G) return GRID_G - 1;
+  return (int)v;
+}
+
+template <typename T, int DIM>
+__global__ void __launch_bounds__(GRIDNN_THREADS) nn_grid_kernel(GridNNArgs a) {
+  const int b = blockIdx.y;
+  if (a.counters && a.counters[1]) return;
+  if (a.frozen && a.frozen[b]) return;
+  __shared__ double sP[12];
+  __shared__ double sG[4];
+  const int tid = threadIdx.x, lane = tid & 31;
+  if (tid < 12) sP[tid] = a.pose[(size_t)b * 12 + tid];
+  if (tid < 4) sG[tid] = a.geom[(size_t)b * 4 + tid];
+  __syncthreads();
+  const int qi = blockIdx.x * GRIDNN_WARPS + (tid >> 5);
+  if (qi >= a.n) return;                                   // whole warp
+
+  const T* src = static_cast<const T*>(a.source) + (size_t)b * a.n * 3;
+  const T* tgt = static_cast<const T*>(a.target) + (size_t)b * a.m * a.cols;
+  const int* start = a.cell_start + (size_t)b * GRID_STRIDE;
+  const SortedPoint<T>* sorted = static_cast<const SortedPoint<T>*>(a.sorted) + (size_t)b * a.m;
+
+  double qx, qy, qz;
+  transform_query<T, DIM>(src + (size_t)qi * 3, sP, qx, qy, qz);
+  double fx = (qx - sG[0]) * sG[2], fy = (qy - sG[1]) * sG[2];
+  fx = fmin(fmax(fx, -1.0e12), 1.0e12); fy = fmin(fmax(fy, -1.0e12), 1.0e12);
+  const bool inside = fx >= 0.0 && fx < (double)GRID_G && fy >= 0.0 && fy < (double)GRID_G;
+  const double gap = inside ? fmin(fmin(fx, (double)GRID_G - fx), fmin(fy, (double)GRID_G - fy)) : 0.0;   // cells
+  constexpr double SLACK = 9.5367431640625e-07;            // 2^-20
+  const double abs_slack = 1.0e-9 * (1.0 + fabs(fx) + fabs(fy));
+
+  double D2 = 1.0e308; int I = INT_MAX;                    // per-lane partial minimum
+  auto scan = [&](int s0, int e0) {
+    for (int p = s0 + lane; p < e0; p += 32) {
+      double tx, ty, tz; int j;
+      load_sorted(sorted + p, tx, ty, tz, j);
+      const double dx = tx - qx, dy = ty - qy;
+      double e2 = fma(dy, dy, __dmul_rn(dx, dx));
+      if (DIM == 3) { const double dz = tz - qz; e2 = fma(dz, dz, e2); }
+      if (e2 < D2 || (e2 == D2 && j < I)) { D2 = e2; I = j; }
+    }
+  };
+  // the cells (x0..x1) x (y0..y1) of level L (at most 3 x 3): lane c fetches the range of cell c,
+  // the warp then walks the ranges one after the other
+  auto scan_cells = [&](int L, int x0, int x1, int y0, int y1) {
+    const int nx = x1 - x0 + 1, nc = nx * (y1 - y0 + 1);
+    int s0 = 0, e0 = 0;
+    if (lane < nc) {
+      const unsigned k = morton2((unsigned)((x0 + lane % nx) << L), (unsigned)((y0 + lane / nx) << L));
+      s0 = __ldg(start + k); e0 = __ldg(start + k + (1u << (2 * L)));
+    }
+    for (int c = 0; c < nc; ++c) scan(__shfl_sync(0xffffffffu, s0, c), __shfl_sync(0xffffffffu, e0, c));
+  };
+  auto scan_outside = [&]() { scan(__ldg(start + GRID_OUTSIDE), __ldg(start + GRID_OUTSIDE + 1)); };
+  // lexicographic (D2, I) minimum over the warp, left in every lane
+  auto reduce = [&]() {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const double d = __shfl_xor_sync(0xffffffffu, D2, o);
+      const int j = __shfl_xor_sync(0xffffffffu, I, o);
+      if (d < D2 || (d == D2 && j < I)) { D2 = d; I = j; }
+    }
+  };
+
+  bool done = false;
+  if (a.idx_prev) {
+    const int j0 = a.idx_prev[(size_t)b * a.n + qi];
+    if (j0 >= 0 && j0 < a.m) {
+      const double d0 = exact_dist2<T, DIM>(tgt + (size_t)j0 * a.cols, qx, qy, qz);
+      if (d0 < 1.0e300) { D2 = d0; I = j0; }
+    }
+  }
+  if (!(D2 < 1.0e300)) {
+    D2 = 1.0e308; I = INT_MAX;
+    const int cx = clamp_cell(fx), cy = clamp_cell(fy);
+    for (int L = 0; L <= GRID_BITS; ++L) {
+      const int nb = GRID_G >> L, bx = cx >> L, by = cy >> L;
+      scan_cells(L, bx > 0 ? bx - 1 : 0, bx + 1 < nb ? bx + 1 : nb - 1, by > 0 ? by - 1 : 0, by + 1 < nb ? by + 1 : nb - 1);
+      reduce();
+      if (D2 < 1.0e300) {
+        const double dc = sqrt(D2) * sG[2] * (1.0 + SLACK) + abs_slack;   // cells, inflated
+        done = inside && dc < (double)(1 << L) && dc < gap;
+        break;
+      }
+      if (nb <= 2) break;                                            // the whole grid has been scanned
+    }
+    if (!(D2 < 1.0e300)) { scan_outside(); reduce(); done = true; }
+  }
+  if (!done) {
+    const double Dc = sqrt(D2) * sG[2] * (1.0 + SLACK) + abs_slack;  // cells, inflated
+    const int xlo = clamp_cell(fx - Dc), xhi = clamp_cell(fx + Dc), ylo = clamp_cell(fy - Dc), yhi = clamp_cell(fy + Dc);
+    int L = 0;
+    while (((xhi >> L) - (xlo >> L)) > 2 || ((yhi >> L) - (ylo >> L)) > 2) ++L;
+    // cells entirely left/right/above/below the square hold nothing (clamping only ADDS cells)
+    if (fx + Dc >= 0.0 && fx - Dc < (double)GRID_G && fy + Dc >= 0.0 && fy - Dc < (double)GRID_G)
+      scan_cells(L, xlo >> L, xhi >> L, ylo >> L, yhi >> L);
+    if (!(fx - Dc >= 0.0 && fx + Dc < (double)GRID_G && fy - Dc >= 0.0 && fy + Dc < (double)GRID_G)) scan_outside();
+    reduce();
+  }
+  if (lane == 0) {
+    const size_t o = (size_t)b * a.n + qi;
+    a.pd2[o] = D2; a.pidx[o] = I;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -1037,6 +1339,40 @@ static int launch_nn(const NNArgs& a, const IcpPlan& pl, cudaStream_t st) {
   return check_launch();
 }
 
+// Cell-grid backend: geometry from the scan footprint at the current pose, counting sort of the
+// targets by Morton cell (count -> scan -> scatter).  Once per forward: the targets do not move.
+template <typename T, int DIM>
+static int build_grid(const void* source, const void* target, int cols, const IcpPlan& pl, const IcpWorkspace& w,
+                      cudaStream_t st) {
+  int rc;
+  grid_geom_kernel<T, DIM><<<pl.N, 256, 0, st>>>(static_cast<const T*>(source), w.pose, pl.n, w.geom);
+  if ((rc = check_launch())) return rc;
+  if (cudaMemsetAsync(w.cell_cursor, 0, (size_t)pl.N * GRID_STRIDE * sizeof(int), st) != cudaSuccess) return check_launch();
+  const size_t total = (size_t)pl.N * pl.m;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  grid_count_kernel<T><<<blocks, 256, 0, st>>>(static_cast<const T*>(target), cols, pl.N, pl.m, w.geom, w.keys, w.cell_cursor);
+  if ((rc = check_launch())) return rc;
+  grid_scan_kernel<<<pl.N, 1024, 0, st>>>(w.cell_cursor, w.cell_start);
+  if ((rc = check_launch())) return rc;
+  grid_scatter_kernel<T><<<blocks, 256, 0, st>>>(static_cast<const T*>(target), cols, pl.N, pl.m, w.keys, w.cell_cursor,
+                                                  static_cast<SortedPoint<T>*>(w.sorted));
+  return check_launch();
+}
+
+template <typename T, int DIM>
+static int launch_grid_nn(const NNArgs& a, const IcpPlan& pl, const IcpWorkspace& w, cudaStream_t st) {
+  GridNNArgs g;
+  g.source = a.source; g.target = a.target; g.pose = a.pose;
+  g.geom = w.geom; g.cell_start = w.cell_start; g.sorted = w.sorted;
+  g.idx_prev = a.idx_prev; g.frozen = a.frozen; g.counters = a.counters;
+  g.pd2 = a.pd2; g.pidx = a.pidx;
+  g.N = pl.N; g.n = pl.n; g.m = pl.m; g.cols = a.cols;
+  dim3 grid((pl.n + GRIDNN_WARPS - 1) / GRIDNN_WARPS, pl.N);
+  nn_grid_kernel<T, DIM><<<grid, GRIDNN_THREADS, 0, st>>>(g);
+  return check_launch();
+}
+
 // Cold start: pack every NN_SUB_STRIDE-th target, then the bound pass over that subsample.
 template <typename T, int DIM>
 static int launch_bound(NNArgs a, const IcpPlan& pl, const IcpWorkspace& w, int dim, cudaStream_t st) {
@@ -1059,7 +1395,7 @@ static int launch_bound(NNArgs a, const IcpPlan& pl, const IcpWorkspace& w, int 
 // recorded on the launch stream between the kernel classes; the normal path records nothing.
 struct ForwardProfile {
   std::vector<cudaEvent_t> ev;     // boundaries
-  std::vector<int> cls;            // class of the interval that ENDS at ev[i+1]: 0 nn, 1 step, 2 other, 3 bound pass
+  std::vector<int> cls;            // class of the interval that ENDS at ev[i+1]: 0 nn, 1 step, 2 other, 3 bound pass, 4 grid build
   cudaStream_t st;
   void mark(int c) {
     cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st);
@@ -1081,7 +1417,11 @@ static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* s
 
   init_state_kernel<T><<<(pl.N + 127) / 128, 128, 0, st>>>(static_cast<const T*>(T_init), w, pl.N);
   if ((rc = check_launch())) return rc;
-  {
+  if (pl.grid) {
+    if (prof) prof->mark(2);
+    if ((rc = build_grid<T, DIM>(source, target, p->target_cols, pl, w, st))) return rc;
+    if (prof) prof->mark(4);
+  } else {
     const size_t total = (size_t)pl.N * pl.mp;
     int blocks = (int)((total + 255) / 256);
     if (blocks > 148 * 16) blocks = 148 * 16;
@@ -1119,7 +1459,7 @@ static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* s
   for (int it = 0; it < p->max_iterations; ++it) {
     na.idx_prev = it > 0 ? w.idx_cur : nullptr;
     if (prof && it == 0 && !pl.sub_stride) prof->mark(2);
-    if ((rc = launch_nn<T, DIM>(na, pl, st))) return rc;
+    if ((rc = pl.grid ? launch_grid_nn<T, DIM>(na, pl, w, st) : launch_nn<T, DIM>(na, pl, st))) return rc;
     if (prof) prof->mark(0);
     sa.it = it;
     icp_step_kernel<T, ICP, DIM><<<pl.N, STEP_THREADS, 0, st>>>(sa);
@@ -1161,6 +1501,7 @@ static int validate(const mmb_icp_params* p) {
   if (p->icp_type != MMB_PT2PL && p->icp_type != MMB_PT2PT) return MMB_ERR_UNSUPPORTED;
   if (p->dim != 2 && p->dim != 3) return MMB_ERR_UNSUPPORTED;
   if (p->loss_kind < 0 || p->loss_kind > 2) return MMB_ERR_UNSUPPORTED;
+  if (p->nn_backend < MMB_NN_AUTO || p->nn_backend > MMB_NN_GRID) return MMB_ERR_UNSUPPORTED;
   return MMB_OK;
 }
 
@@ -1178,6 +1519,41 @@ static int validate(const mmb_icp_params* p) {
       default: return FN<double, MMB_PT2PT, 3>(__VA_ARGS__);                                           \
     }                                                                                                  \
   } while (0)
+
+template <typename T, int DIM>
+static int run_nn_search(const IcpPlan& pl, int cols, int dim, const void* query, const void* target, int32_t* idx_out,
+                         const IcpWorkspace& w, cudaStream_t st) {
+  int rc;
+  identity_pose_kernel<<<(pl.N + 127) / 128, 128, 0, st>>>(w.pose, pl.N);
+  if ((rc = check_launch())) return rc;
+  NNArgs na;
+  na.source = query; na.target = target; na.pose = w.pose;
+  na.tx = w.tx; na.ty = w.ty; na.tz = w.tz; na.tn = w.tn;
+  na.idx_prev = nullptr; na.frozen = nullptr; na.counters = nullptr;
+  na.bound_in = nullptr; na.bound_out = nullptr; na.bound_S = 0;
+  na.pd2 = w.pd2; na.pidx = w.pidx;
+  na.N = pl.N; na.n = pl.n; na.m = pl.m; na.mp = pl.mp; na.cols = cols;
+  na.tiles_per_slice = pl.tiles_per_slice; na.S = pl.S;
+  if (pl.grid) {
+    if ((rc = build_grid<T, DIM>(query, target, cols, pl, w, st))) return rc;
+    if ((rc = launch_grid_nn<T, DIM>(na, pl, w, st))) return rc;
+  } else {
+    const size_t total = (size_t)pl.N * pl.mp;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    pack_targets_kernel<T><<<blocks, 256, 0, st>>>(static_cast<const T*>(target), cols, pl.N, pl.m, pl.m, pl.mp, 1, dim,
+                                                    w.tx, w.ty, w.tz, w.tn);
+    if ((rc = check_launch())) return rc;
+    if (pl.sub_stride) {
+      if ((rc = launch_bound<T, DIM>(na, pl, w, dim, st))) return rc;
+      na.bound_in = w.bound; na.bound_S = pl.S_sub;
+    }
+    if ((rc = launch_nn<T, DIM>(na, pl, st))) return rc;
+  }
+  const size_t nq = (size_t)pl.N * pl.n;
+  merge_only_kernel<<<(int)((nq + 255) / 256), 256, 0, st>>>(w.pd2, w.pidx, pl.S, pl.N, pl.n, idx_out);
+  return check_launch();
+}
 
 }  // namespace mmb
 
@@ -1204,13 +1580,13 @@ const char* mmb_last_cuda_error(void) { return g_last_cuda_error; }
 
 size_t mmb_icp_workspace_bytes(const mmb_icp_params* p) {
   if (validate(p)) return 0;
-  const IcpPlan pl = make_plan(p->N, p->n, p->m, p->icp_type, p->dim, p->nn_slices);
+  const IcpPlan pl = make_plan(p->N, p->n, p->m, p->icp_type, p->dim, p->nn_slices, p->nn_backend, p->dtype);
   return carve_workspace(nullptr, pl).bytes;
 }
 
 size_t mmb_icp_saved_bytes(const mmb_icp_params* p) {
   if (validate(p) || !p->save_for_backward) return 0;
-  const IcpPlan pl = make_plan(p->N, p->n, p->m, p->icp_type, p->dim, p->nn_slices);
+  const IcpPlan pl = make_plan(p->N, p->n, p->m, p->icp_type, p->dim, p->nn_slices, p->nn_backend, p->dtype);
   return carve_saved(nullptr, pl, p->max_iterations).bytes;
 }
 
@@ -1227,7 +1603,7 @@ static int icp_forward_impl(const mmb_icp_params* p, const void* source, const v
   if (p->has_weight && !weight) return MMB_ERR_NULL_POINTER;
   if (p->save_for_backward && !saved) return MMB_ERR_NULL_POINTER;
   if (reinterpret_cast<uintptr_t>(workspace) % 256) return MMB_ERR_MISALIGNED;
-  const IcpPlan pl = make_plan(p->N, p->n, p->m, p->icp_type, p->dim, p->nn_slices);
+  const IcpPlan pl = make_plan(p->N, p->n, p->m, p->icp_type, p->dim, p->nn_slices, p->nn_backend, p->dtype);
   if (workspace_bytes < carve_workspace(nullptr, pl).bytes) return MMB_ERR_WORKSPACE_TOO_SMALL;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   MMB_DISPATCH(p, run_forward, p, pl, source, target, T_init, weight, T_out, pc_out, deltas, weights_hist, costs,
@@ -1251,7 +1627,7 @@ int mmb_icp_forward_profiled(const mmb_icp_params* p, const void* source, const 
   ForwardProfile prof;
   int rc = icp_forward_impl(p, source, target, T_init, weight, T_out, pc_out, deltas, weights_hist, costs, converged,
                             iterations, matched_ratio, iters_done, saved, workspace, workspace_bytes, stream, &prof);
-  for (int c = 0; c < 4; ++c) { host_ms[c] = 0.f; host_launches[c] = 0; }
+  for (int c = 0; c < MMB_PROFILE_CLASSES; ++c) { host_ms[c] = 0.f; host_launches[c] = 0; }
   if (!prof.ev.empty()) {
     if (cudaEventSynchronize(prof.ev.back()) != cudaSuccess && rc == MMB_OK) rc = MMB_ERR_CUDA;
     for (size_t i = 0; i + 1 < prof.ev.size(); ++i) {
@@ -1273,61 +1649,36 @@ int mmb_icp_backward(const mmb_icp_params* p, const void* source, const void* ta
   int rc = validate(p);
   if (rc) return rc;
   if (!source || !target || !saved) return MMB_ERR_NULL_POINTER;
-  const IcpPlan pl = make_plan(p->N, p->n, p->m, p->icp_type, p->dim, p->nn_slices);
+  const IcpPlan pl = make_plan(p->N, p->n, p->m, p->icp_type, p->dim, p->nn_slices, p->nn_backend, p->dtype);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   MMB_DISPATCH(p, run_backward, p, pl, source, target, weight, saved, grad_T, grad_pc, grad_source, grad_target,
                grad_T_init, grad_weight, st);
 }
 
-size_t mmb_nn_workspace_bytes(int32_t N, int32_t n, int32_t m, int32_t nn_slices) {
+size_t mmb_nn_workspace_bytes(int32_t N, int32_t n, int32_t m, int32_t dtype, int32_t nn_slices, int32_t nn_backend) {
   if (N <= 0 || n <= 0 || m <= 0) return 0;
-  const IcpPlan pl = make_plan(N, n, m, MMB_PT2PL, 3, nn_slices);
+  const IcpPlan pl = make_plan(N, n, m, MMB_PT2PL, 3, nn_slices, nn_backend, dtype);
   return carve_workspace(nullptr, pl).bytes;
 }
 
 int mmb_nn_search(int32_t N, int32_t n, int32_t m, int32_t target_cols, int32_t dtype, int32_t dim,
-                  int32_t nn_slices, const void* query, const void* target, int32_t* idx_out, void* workspace,
-                  size_t workspace_bytes, void* stream) {
+                  int32_t nn_slices, int32_t nn_backend, const void* query, const void* target, int32_t* idx_out,
+                  void* workspace, size_t workspace_bytes, void* stream) {
   if (N <= 0 || n <= 0 || m <= 0 || (target_cols != 3 && target_cols != 6)) return MMB_ERR_INVALID_SHAPE;
   if (dtype != MMB_F32 && dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
   if (dim != 2 && dim != 3) return MMB_ERR_UNSUPPORTED;
+  if (nn_backend < MMB_NN_AUTO || nn_backend > MMB_NN_GRID) return MMB_ERR_UNSUPPORTED;
   if (!query || !target || !idx_out || !workspace) return MMB_ERR_NULL_POINTER;
   if (reinterpret_cast<uintptr_t>(workspace) % 256) return MMB_ERR_MISALIGNED;
-  const IcpPlan pl = make_plan(N, n, m, MMB_PT2PL, 3, nn_slices);
+  const IcpPlan pl = make_plan(N, n, m, MMB_PT2PL, 3, nn_slices, nn_backend, dtype);
   IcpWorkspace w = carve_workspace(workspace, pl);
   if (workspace_bytes < w.bytes) return MMB_ERR_WORKSPACE_TOO_SMALL;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  int rc;
-  identity_pose_kernel<<<(N + 127) / 128, 128, 0, st>>>(w.pose, N);
-  if ((rc = check_launch())) return rc;
-  const size_t total = (size_t)N * pl.mp;
-  int blocks = (int)((total + 255) / 256);
-  if (blocks > 148 * 16) blocks = 148 * 16;
   if (dtype == MMB_F32)
-    pack_targets_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(target), target_cols, N, m, m, pl.mp, 1, dim, w.tx, w.ty, w.tz, w.tn);
-  else
-    pack_targets_kernel<double><<<blocks, 256, 0, st>>>(static_cast<const double*>(target), target_cols, N, m, m, pl.mp, 1, dim, w.tx, w.ty, w.tz, w.tn);
-  if ((rc = check_launch())) return rc;
-  NNArgs na;
-  na.source = query; na.target = target; na.pose = w.pose;
-  na.tx = w.tx; na.ty = w.ty; na.tz = w.tz; na.tn = w.tn;
-  na.idx_prev = nullptr; na.frozen = nullptr; na.counters = nullptr;
-  na.bound_in = nullptr; na.bound_out = nullptr; na.bound_S = 0;
-  na.pd2 = w.pd2; na.pidx = w.pidx;
-  na.N = N; na.n = n; na.m = m; na.mp = pl.mp; na.cols = target_cols;
-  na.tiles_per_slice = pl.tiles_per_slice; na.S = pl.S;
-  if (pl.sub_stride) {
-    if (dtype == MMB_F32) rc = dim == 2 ? launch_bound<float, 2>(na, pl, w, dim, st) : launch_bound<float, 3>(na, pl, w, dim, st);
-    else rc = dim == 2 ? launch_bound<double, 2>(na, pl, w, dim, st) : launch_bound<double, 3>(na, pl, w, dim, st);
-    if (rc) return rc;
-    na.bound_in = w.bound; na.bound_S = pl.S_sub;
-  }
-  if (dtype == MMB_F32) rc = dim == 2 ? launch_nn<float, 2>(na, pl, st) : launch_nn<float, 3>(na, pl, st);
-  else rc = dim == 2 ? launch_nn<double, 2>(na, pl, st) : launch_nn<double, 3>(na, pl, st);
-  if (rc) return rc;
-  const size_t nq = (size_t)N * n;
-  merge_only_kernel<<<(int)((nq + 255) / 256), 256, 0, st>>>(w.pd2, w.pidx, pl.S, N, n, idx_out);
-  return check_launch();
+    return dim == 2 ? run_nn_search<float, 2>(pl, target_cols, dim, query, target, idx_out, w, st)
+                    : run_nn_search<float, 3>(pl, target_cols, dim, query, target, idx_out, w, st);
+  return dim == 2 ? run_nn_search<double, 2>(pl, target_cols, dim, query, target, idx_out, w, st)
+                  : run_nn_search<double, 3>(pl, target_cols, dim, query, target, idx_out, w, st);
 }
 
 int mmb_fp32_probe(int32_t blocks, int32_t iters, int32_t packed, float* out, void* stream) {

@@ -56,6 +56,7 @@ class _IcpFunction(torch.autograd.Function):
         p.has_weight = int(weight is not None)
         p.save_for_backward = int(needs_grad)
         p.nn_slices = int(cfg.get("nn_slices", 0))
+        p.nn_backend = int(cfg.get("nn_backend", _capi.NN_AUTO))
         p.tolerance = float(cfg["tolerance"])
         p.tanh_steepness = float(cfg["tanh_steepness"])
         p.match_ratio_thresh = float(cfg["match_ratio_thresh"])
@@ -133,6 +134,7 @@ class ICP:
         self.match_ratio_thresh = self.config['dICP']['logging']['matched_ratio_thresh']
         self.diff = differentiable
         self.nn_slices = 0          # 0: the library picks the target split of the NN search
+        self.nn_backend = _capi.NN_AUTO   # exact cell grid for large maps, brute force otherwise (same indices)
 
         use_gumbel = self.config['dICP']['functionality']['gumbel']
         if use_gumbel:
@@ -178,7 +180,8 @@ class ICP:
                    differentiable=bool(self.diff), const_iter=bool(self.const_iter), trim_dist=trim_dist,
                    loss_kind=loss_kind, loss_metric=loss_metric, dim=int(dim),
                    tanh_steepness=self.config['dICP']['parameters']['tanh_steepness'],
-                   match_ratio_thresh=self.match_ratio_thresh, nn_slices=self.nn_slices)
+                   match_ratio_thresh=self.match_ratio_thresh, nn_slices=self.nn_slices,
+                   nn_backend=self.nn_backend)
         T, pc, deltas, weights, costs, converged, iterations, matched, iters_done = _IcpFunction.apply(
             source.to(dev), target.to(dev), T_init.to(dev), weight_arg, cfg)
 

@@ -13,7 +13,8 @@ import torch
 from .. import _capi
 
 
-def nearest_index(x: torch.Tensor, y: torch.Tensor, dim: int = 3, nn_slices: int = 0) -> torch.Tensor:
+def nearest_index(x: torch.Tensor, y: torch.Tensor, dim: int = 3, nn_slices: int = 0,
+                  nn_backend: int = _capi.NN_AUTO) -> torch.Tensor:
     """(N,n) int64 index of the nearest row of y (N,m,3|6) for every row of x (N,n,3)."""
     _capi.require_cuda()
     lib = _capi.load_library()
@@ -25,11 +26,12 @@ def nearest_index(x: torch.Tensor, y: torch.Tensor, dim: int = 3, nn_slices: int
     N, n, _ = xq.shape
     m, cols = yt.shape[1], yt.shape[2]
     with torch.cuda.device(dev):
-        ws_bytes = lib.mmb_nn_workspace_bytes(N, n, m, nn_slices)
+        dt = _capi.F32 if xq.dtype == torch.float32 else _capi.F64
+        ws_bytes = lib.mmb_nn_workspace_bytes(N, n, m, dt, nn_slices, nn_backend)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         idx = torch.empty((N, n), dtype=torch.int32, device=dev)
-        rc = lib.mmb_nn_search(N, n, m, cols, _capi.F32 if xq.dtype == torch.float32 else _capi.F64, dim,
-                               nn_slices, _capi.ptr(xq), _capi.ptr(yt), _capi.ptr(idx), _capi.ptr(ws), ws_bytes,
+        rc = lib.mmb_nn_search(N, n, m, cols, dt, dim,
+                               nn_slices, nn_backend, _capi.ptr(xq), _capi.ptr(yt), _capi.ptr(idx), _capi.ptr(ws), ws_bytes,
                                _capi.stream_ptr())
         _capi.check(rc, "mmb_nn_search")
     return idx.to(torch.int64).to(x.device)

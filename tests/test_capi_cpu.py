@@ -47,7 +47,7 @@ def test_every_declared_symbol_is_exported_and_bound(lib):
 
 
 def test_status_strings(lib):
-    assert lib.mmb_abi_version() == 1
+    assert lib.mmb_abi_version() == 2
     assert lib.mmb_status_string(0) == b"ok"
     assert lib.mmb_status_string(4) == b"workspace too small"
     assert lib.mmb_status_string(99) == b"unknown status"
@@ -83,11 +83,11 @@ def test_icp_argument_validation_runs_before_cuda(lib):
 
 
 def test_nn_argument_validation(lib):
-    assert lib.mmb_nn_workspace_bytes(1, 10, 10, 0) > 0
-    assert lib.mmb_nn_workspace_bytes(0, 10, 10, 0) == 0
-    assert lib.mmb_nn_search(1, 10, 10, 4, 0, 3, 0, None, None, None, None, 0, None) == 2
-    assert lib.mmb_nn_search(1, 10, 10, 3, 0, 3, 0, None, None, None, None, 0, None) == 1
-    assert lib.mmb_nn_search(1, 10, 10, 3, 5, 3, 0, None, None, None, None, 0, None) == 3
+    assert lib.mmb_nn_workspace_bytes(1, 10, 10, 0, 0, 0) > 0
+    assert lib.mmb_nn_workspace_bytes(0, 10, 10, 0, 0, 0) == 0
+    assert lib.mmb_nn_search(1, 10, 10, 4, 0, 3, 0, 0, None, None, None, None, 0, None) == 2
+    assert lib.mmb_nn_search(1, 10, 10, 3, 0, 3, 0, 0, None, None, None, None, 0, None) == 1
+    assert lib.mmb_nn_search(1, 10, 10, 3, 5, 3, 0, 0, None, None, None, None, 0, None) == 3
 
 
 def test_product_refuses_to_run_without_cuda():

@@ -112,8 +112,8 @@ def _replay_queries(d, meta, k):
 
 
 @pytest.mark.parametrize("name", FIXTURE[:2] + SYNTH)
-@pytest.mark.parametrize("slices", [0, 3])
-def test_correspondence_indices_bit_exact(name, slices, golden):
+@pytest.mark.parametrize("slices,backend", [(0, 1), (3, 1), (0, 2)])
+def test_correspondence_indices_bit_exact(name, slices, backend, golden):
     """Indices of every iteration equal the reference's (exact-difference cdist, fp64)."""
     from mm_masking_b200.dICP.nn import nearest_index
     d, meta = golden(name)
@@ -123,7 +123,7 @@ def test_correspondence_indices_bit_exact(name, slices, golden):
     ref_idx = d["ref_indices"]
     for k in range(ref_idx.shape[0]):
         q = _replay_queries(d, meta, k).cuda()
-        idx = nearest_index(q, tgt, dim=meta["dim"], nn_slices=slices).cpu().numpy()
+        idx = nearest_index(q, tgt, dim=meta["dim"], nn_slices=slices, nn_backend=backend).cpu().numpy()
         mism = int((idx != ref_idx[k]).sum())
         assert mism == 0, f"iteration {k}: {mism} of {idx.size} indices differ"
 
@@ -141,3 +141,28 @@ def test_known_answer_pose(golden):
         out["T"].sum().backward()
         assert src.grad is not None and tgt.grad is not None
         assert not torch.isnan(src.grad).any() and not torch.isnan(tgt.grad).any()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+@pytest.mark.parametrize("cfg", [("pt2pl", 2, False), ("pt2pl", 3, True), ("pt2pt", 2, False)])
+def test_cell_grid_backend_equals_brute_force(dtype, cfg):
+    """The two NN backends return the same indices, so every output and gradient of the whole ICP
+    call is bit-identical (cold start at iteration 0, warm starts afterwards, frozen pairs)."""
+    from mm_masking_b200 import synth, _capi
+    from mm_masking_b200.dICP import ICP
+    icp_type, dim, three_d = cfg
+    batch = synth.make_icp_batch(N=3, n=500, m=9000, seed=11, three_d=three_d)
+    res = []
+    for backend in (_capi.NN_BRUTE, _capi.NN_GRID):
+        tt = lambda a: torch.tensor(a, dtype=dtype, device="cuda")
+        src, T0 = tt(batch["source"]).requires_grad_(True), tt(batch["T_init"]).requires_grad_(True)
+        tgt = tt(batch["target"] if icp_type == "pt2pl" else batch["target"][..., :3])
+        w = tt(batch["weight"]).requires_grad_(True)
+        alg = ICP(icp_type=icp_type, differentiable=True, max_iterations=12, tolerance=1e-4)
+        alg.nn_backend = backend
+        out = alg.icp(src, tgt, T0, weight=w, trim_dist=5.0, loss_fn={"name": "cauchy", "metric": 1.0}, dim=dim)
+        (out["T"].sum() + out["pc"].sum()).backward()
+        res.append([out["T"], out["pc"], out["deltas"], out["weights"], out["costs"], out["stats"]["iterations"],
+                    src.grad, T0.grad, w.grad])
+    for a, b in zip(*res):
+        assert torch.equal(a, b)

@@ -43,8 +43,8 @@ def test_exact_ties_take_the_lowest_index(dtype, dim):
     q[:, ::2] += 0.01
     if dim == 2:
         q[:, :, 2] = 0
-    for slices in (0, 2, 5):
-        idx = nearest_index(q.cuda(), tgt.cuda(), dim=dim, nn_slices=slices).cpu()
+    for slices, backend in ((0, 1), (2, 1), (5, 1), (0, 2)):
+        idx = nearest_index(q.cuda(), tgt.cuda(), dim=dim, nn_slices=slices, nn_backend=backend).cpu()
         ref = O.nearest_index(q.double(), tgt.double(), "exact")
         assert torch.equal(idx, ref)
         assert int(idx.max()) < 1250                                   # always the first copy
@@ -61,11 +61,13 @@ def test_random_clouds_match_oracle(shape, dtype):
     if m > 10:
         tgt[:, -m // 10:, :] = 80000.0                                  # padding rows (ICP.py:446)
     for dim in (2, 3):
-        idx = nearest_index(q.cuda(), tgt.cuda(), dim=dim).cpu()
         qq, tt = q.double().clone(), tgt[:, :, :3].double().clone()
         if dim == 2:
             qq[:, :, 2] = 0; tt[:, :, 2] = 0
-        assert torch.equal(idx, O.nearest_index(qq, tt, "exact"))
+        ref = O.nearest_index(qq, tt, "exact")
+        for backend in (0, 1, 2):                                       # auto, brute force, cell grid
+            idx = nearest_index(q.cuda(), tgt.cuda(), dim=dim, nn_backend=backend).cpu()
+            assert torch.equal(idx, ref), f"backend {backend}"
 
 
 def test_clustered_near_ties_fp64_queries():
@@ -77,8 +79,9 @@ def test_clustered_near_ties_fp64_queries():
     centers = torch.rand((N, m // 8, 3), generator=g, dtype=torch.float64) * 150 - 75
     tgt = centers.repeat_interleave(8, dim=1) + 1e-6 * torch.randn((N, m, 3), generator=g, dtype=torch.float64)
     q = centers[:, :n] + 1e-3 * torch.randn((N, n, 3), generator=g, dtype=torch.float64)
-    idx = nearest_index(q.cuda(), tgt.cuda(), dim=3).cpu()
-    assert torch.equal(idx, O.nearest_index(q, tgt, "exact"))
+    for backend in (1, 2):
+        idx = nearest_index(q.cuda(), tgt.cuda(), dim=3, nn_backend=backend).cpu()
+        assert torch.equal(idx, O.nearest_index(q, tgt, "exact"))
 
 
 def test_cold_start_bound_pass_keeps_every_tie():
@@ -95,6 +98,32 @@ def test_cold_start_bound_pass_keeps_every_tie():
     q = centers[:, :n] + 1e-3 * torch.randn((N, n, 3), generator=g, dtype=torch.float64)
     for dtype in (torch.float64, torch.float32):
         qq, tt = q.to(dtype), tgt.to(dtype)
-        for slices in (0, 3):
-            idx = nearest_index(qq.cuda(), tt.cuda(), dim=3, nn_slices=slices).cpu()
+        for slices, backend in ((0, 1), (3, 1), (0, 2)):
+            idx = nearest_index(qq.cuda(), tt.cuda(), dim=3, nn_slices=slices, nn_backend=backend).cpu()
             assert torch.equal(idx, O.nearest_index(qq.double(), tt.double(), "exact"))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_cell_grid_clamped_cells_and_far_queries(dtype):
+    """Cell-grid backend corner cases: the grid covers the QUERY footprint, so map points far outside
+    it (pad rows, a distant wall) are clamped into border cells and queries far from every target
+    must climb the levels; the answer must still be the brute-force one."""
+    from mm_masking_b200.dICP.nn import nearest_index
+    g = torch.Generator().manual_seed(33)
+    N, n, m = 3, 300, 9000
+    q = (torch.rand((N, n, 3), generator=g, dtype=torch.float64) * 20 - 10)          # footprint 20 m
+    tgt = torch.empty((N, m, 3), dtype=torch.float64)
+    tgt[0] = torch.rand((m, 3), generator=g, dtype=torch.float64) * 400 - 200          # mostly outside the grid
+    tgt[1] = torch.rand((m, 3), generator=g, dtype=torch.float64) * 2 + 300            # everything in one corner
+    tgt[2] = torch.rand((m, 3), generator=g, dtype=torch.float64) * 30 - 15
+    tgt[2, ::3] = 1.0e5                                                               # pad rows
+    q[2, :10] = 5000.0                                                                # queries off the grid
+    q[2, 10:20] = 0.0                                                                 # zero-padded source rows
+    q, tgt = q.to(dtype), tgt.to(dtype)
+    for dim in (2, 3):
+        qq, tt = q.double().clone(), tgt.double().clone()
+        if dim == 2:
+            qq[:, :, 2] = 0; tt[:, :, 2] = 0
+        ref = O.nearest_index(qq, tt, "exact")
+        idx = nearest_index(q.cuda(), tgt.cuda(), dim=dim, nn_backend=2).cpu()
+        assert torch.equal(idx, ref)
