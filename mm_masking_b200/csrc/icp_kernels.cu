@@ -692,6 +692,12 @@ struct GridNNArgs {
 //     target; that gives D for the square scan (skipped when D is already below the block's cell
 //     size and below the distance to the grid border: nothing outside the block can win or tie).
 constexpr int GRIDNN_WARPS = GRIDNN_THREADS / 32;
+constexpr int GRID_SPLIT = 64;
+
+// an upper bound of sqrt(v), v >= 0, within 2^-22 relative (one MUFU instead of the fp64 routine)
+__device__ __forceinline__ double sqrt_upper(double v) {
+  return (double)__fsqrt_ru(__double2float_ru(v));
+}
 
 __device__ __forceinline__ int clamp_cell(double v) {
   if (!(v >= 0.0)) return 0;
@@ -739,15 +745,44 @@ __global__ void __launch_bounds__(GRIDNN_THREADS) nn_grid_kernel(GridNNArgs a) {
     }
   };
   // the cells (x0..x1) x (y0..y1) of level L (at most 3 x 3): lane c fetches the range of cell c,
-  // the warp then walks the ranges one after the other
-  auto scan_cells = [&](int L, int x0, int x1, int y0, int y1) {
+  // the warp then walks the ranges one after the other.  A cell of level >= 2 holding more than
+  // GRID_SPLIT targets is split into its 4 x 4 sub-cells (16 consecutive Morton sub-ranges) and
+  // only the sub-cells within dc2 (squared bound, cell units) of the query are scanned, runs of
+  // adjacent sub-ranges in one go.
+  auto scan_cells = [&](int L, int x0, int x1, int y0, int y1, double dc2) {
     const int nx = x1 - x0 + 1, nc = nx * (y1 - y0 + 1);
-    int s0 = 0, e0 = 0;
+    const int iy = nx == 1 ? lane : (nx == 2 ? lane >> 1 : (lane * 11) >> 5), ix = lane - nx * iy;
+    int s0 = 0, e0 = 0; unsigned k = 0;
     if (lane < nc) {
-      const unsigned k = morton2((unsigned)((x0 + lane % nx) << L), (unsigned)((y0 + lane / nx) << L));
+      k = morton2((unsigned)((x0 + ix) << L), (unsigned)((y0 + iy) << L));
       s0 = __ldg(start + k); e0 = __ldg(start + k + (1u << (2 * L)));
     }
-    for (int c = 0; c < nc; ++c) scan(__shfl_sync(0xffffffffu, s0, c), __shfl_sync(0xffffffffu, e0, c));
+    unsigned big = L >= 2 ? __ballot_sync(0xffffffffu, e0 - s0 > GRID_SPLIT) : 0u;
+    unsigned small = __ballot_sync(0xffffffffu, e0 > s0) & ~big;
+    while (small) {
+      const int c = __ffs(small) - 1; small &= small - 1;
+      scan(__shfl_sync(0xffffffffu, s0, c), __shfl_sync(0xffffffffu, e0, c));
+    }
+    while (big) {
+      const int c = __ffs(big) - 1; big &= big - 1;
+      const unsigned kc = __shfl_sync(0xffffffffu, k, c);
+      const int icy = nx == 1 ? c : (nx == 2 ? c >> 1 : (c * 11) >> 5), icx = c - nx * icy;
+      const int ss = 1 << (L - 2);                                       // sub-cell size in finest cells
+      int bnd = 0;
+      if (lane <= 16) bnd = __ldg(start + kc + (unsigned)lane * (1u << (2 * (L - 2))));
+      const int bnd_hi = __shfl_down_sync(0xffffffffu, bnd, 1);
+      // Morton sub-index (lane) -> (u, v)
+      const int u = (lane & 1) | ((lane >> 1) & 2), v = ((lane >> 1) & 1) | ((lane >> 2) & 2);
+      const double X = (double)(((x0 + icx) << L) + u * ss), Y = (double)(((y0 + icy) << L) + v * ss);
+      const double dx = fmax(fmax(X - fx, fx - (X + (double)ss)), 0.0), dy = fmax(fmax(Y - fy, fy - (Y + (double)ss)), 0.0);
+      unsigned keep = __ballot_sync(0xffffffffu, lane < 16 && bnd_hi > bnd && fma(dx, dx, dy * dy) <= dc2);
+      while (keep) {
+        const int t0 = __ffs(keep) - 1;
+        const int len = __ffs(~(keep >> t0)) - 1;                        // run of adjacent sub-cells
+        scan(__shfl_sync(0xffffffffu, bnd, t0), __shfl_sync(0xffffffffu, bnd, t0 + len));
+        keep &= ~(((1u << len) - 1u) << t0);
+      }
+    }
   };
   auto scan_outside = [&]() { scan(__ldg(start + GRID_OUTSIDE), __ldg(start + GRID_OUTSIDE + 1)); };
   // lexicographic (D2, I) minimum over the warp, left in every lane
@@ -773,10 +808,10 @@ __global__ void __launch_bounds__(GRIDNN_THREADS) nn_grid_kernel(GridNNArgs a) {
     const int cx = clamp_cell(fx), cy = clamp_cell(fy);
     for (int L = 0; L <= GRID_BITS; ++L) {
       const int nb = GRID_G >> L, bx = cx >> L, by = cy >> L;
-      scan_cells(L, bx > 0 ? bx - 1 : 0, bx + 1 < nb ? bx + 1 : nb - 1, by > 0 ? by - 1 : 0, by + 1 < nb ? by + 1 : nb - 1);
+      scan_cells(L, bx > 0 ? bx - 1 : 0, bx + 1 < nb ? bx + 1 : nb - 1, by > 0 ? by - 1 : 0, by + 1 < nb ? by + 1 : nb - 1, 1.0e300);
       reduce();
       if (D2 < 1.0e300) {
-        const double dc = sqrt(D2) * sG[2] * (1.0 + SLACK) + abs_slack;   // cells, inflated
+        const double dc = sqrt_upper(D2) * sG[2] * (1.0 + SLACK) + abs_slack;   // cells, inflated
         done = inside && dc < (double)(1 << L) && dc < gap;
         break;
       }
@@ -785,13 +820,13 @@ __global__ void __launch_bounds__(GRIDNN_THREADS) nn_grid_kernel(GridNNArgs a) {
     if (!(D2 < 1.0e300)) { scan_outside(); reduce(); done = true; }
   }
   if (!done) {
-    const double Dc = sqrt(D2) * sG[2] * (1.0 + SLACK) + abs_slack;  // cells, inflated
+    const double Dc = sqrt_upper(D2) * sG[2] * (1.0 + SLACK) + abs_slack;  // cells, inflated
     const int xlo = clamp_cell(fx - Dc), xhi = clamp_cell(fx + Dc), ylo = clamp_cell(fy - Dc), yhi = clamp_cell(fy + Dc);
     int L = 0;
     while (((xhi >> L) - (xlo >> L)) > 2 || ((yhi >> L) - (ylo >> L)) > 2) ++L;
     // cells entirely left/right/above/below the square hold nothing (clamping only ADDS cells)
     if (fx + Dc >= 0.0 && fx - Dc < (double)GRID_G && fy + Dc >= 0.0 && fy - Dc < (double)GRID_G)
-      scan_cells(L, xlo >> L, xhi >> L, ylo >> L, yhi >> L);
+      scan_cells(L, xlo >> L, xhi >> L, ylo >> L, yhi >> L, Dc * Dc);
     if (!(fx - Dc >= 0.0 && fx + Dc < (double)GRID_G && fy - Dc >= 0.0 && fy + Dc < (double)GRID_G)) scan_outside();
     reduce();
   }
