@@ -13,10 +13,13 @@ configs[2]): 32 pairs per GPU, 2 000 radar points vs 50 000 lidar map points, 10
   value  pairs/s with inputs resident in HBM (CUDA events per step, L2 flushed between steps)
   e2e    pairs/s through the same public call with HOST (pinned) inputs: H2D of source, target,
          T_init, weight and D2H of T and d(loss)/d(weight) inside the timed region
-  roofline       the nearest-neighbour kernel (nn_search_kernel): 8 flop per (source, target)
-                 pair per launch / its CUDA-event duration, against the FP32 FMA-pipe rate
-                 measured in the same run by mmb_fp32_probe (MEASURED_PEAKS.json has no
-                 CUDA-core FP32 figure)
+  roofline       the dominant kernel of the default path, the exact cell-grid search
+                 (nn_grid_kernel): algorithmic bytes per launch / its CUDA-event duration against
+                 the measured HBM peak, flagged work-avoiding
+  roofline_exhaustive_nn   the exhaustive kernel (nn_search_kernel, --nn-backend brute) on the
+                 same data in the same run: 8 flop per (source, target) pair per launch / its
+                 CUDA-event duration, against the FP32 FMA-pipe rate measured in the same run by
+                 mmb_fp32_probe (MEASURED_PEAKS.json has no CUDA-core FP32 figure)
   cpu_baseline   the oracle port of the reference algorithm (torch CPU, `torch.cdist` +
                  `argmin` exactly as `external/dICP/dICP/nn.py:32-38`) on the box's host cores
 
@@ -239,41 +242,48 @@ def run_ours(args, wl, rank, world, local_rank):
         return
 
     # ---- roofline of the dominant kernel: per-class CUDA-event timing of the same forward -----
-    p = _capi.IcpParams()
-    p.N, p.n, p.m, p.target_cols = N, n, m, 6
-    p.dtype, p.icp_type, p.dim, p.max_iterations = _capi.F32, _capi.PT2PL, wl["dim"], K
-    p.differentiable, p.const_iter, p.use_trim, p.trim_dist = 1, 1, 1, 5.0
-    p.loss_kind, p.loss_metric, p.has_weight, p.save_for_backward = _capi.LOSS_CAUCHY, 1.0, 1, 1
-    p.tolerance, p.tanh_steepness, p.match_ratio_thresh = 1e-5, 5.0, 0.1
-    p.nn_slices = args.nn_slices
-    p.nn_backend = NN_BACKENDS[args.nn_backend]
-    ws_bytes, sv_bytes = lib.mmb_icp_workspace_bytes(p), lib.mmb_icp_saved_bytes(p)
-    f32 = dict(dtype=torch.float32, device=dev)
-    bufs = dict(ws=torch.empty(ws_bytes, dtype=torch.uint8, device=dev), sv=torch.empty(sv_bytes, dtype=torch.uint8, device=dev),
-                T=torch.empty((N, 4, 4), **f32), pc=torch.empty((N, n, 3), **f32), de=torch.zeros((N, K, 6), **f32),
-                wh=torch.zeros((N, K, n), **f32), co=torch.zeros((N, K), **f32),
-                cv=torch.zeros(N, dtype=torch.uint8, device=dev), it=torch.zeros(N, **f32), mr=torch.zeros(N, **f32),
-                idn=torch.zeros(1, dtype=torch.int32, device=dev))
     NC = _capi.PROFILE_CLASSES
-    ms3, cnt3 = (C.c_float * NC)(), (C.c_int32 * NC)()
-    acc_ms, acc_n = [0.0] * NC, [0] * NC
+    f32 = dict(dtype=torch.float32, device=dev)
     w_det = d_w.detach()
-    for rep in range(2 + min(args.steps, 5)):
-        flush.fill_(1)
-        rc = lib.mmb_icp_forward_profiled(p, _capi.ptr(d_src), _capi.ptr(d_tgt), _capi.ptr(d_T0), _capi.ptr(w_det),
-                                          _capi.ptr(bufs["T"]), _capi.ptr(bufs["pc"]), _capi.ptr(bufs["de"]),
-                                          _capi.ptr(bufs["wh"]), _capi.ptr(bufs["co"]), _capi.ptr(bufs["cv"]),
-                                          _capi.ptr(bufs["it"]), _capi.ptr(bufs["mr"]), _capi.ptr(bufs["idn"]),
-                                          _capi.ptr(bufs["sv"]), _capi.ptr(bufs["ws"]), ws_bytes, _capi.stream_ptr(),
-                                          ms3, cnt3)
-        _capi.check(rc, "mmb_icp_forward_profiled")
-        if rep >= 2:
-            for c in range(NC):
-                acc_ms[c] += ms3[c]; acc_n[c] += cnt3[c]
-    nn_ms = acc_ms[0] / max(acc_n[0], 1)            # average duration of one NN launch
-    step_ms = acc_ms[1] / max(acc_n[1], 1)
-    reps = max(1, acc_n[0] // K)
-    fwd_ms = sum(acc_ms) / reps
+
+    def profile_forward(backend):
+        """mean ms per launch of each kernel class (mmb_icp_forward_profiled, events on the launch stream)"""
+        p = _capi.IcpParams()
+        p.N, p.n, p.m, p.target_cols = N, n, m, 6
+        p.dtype, p.icp_type, p.dim, p.max_iterations = _capi.F32, _capi.PT2PL, wl["dim"], K
+        p.differentiable, p.const_iter, p.use_trim, p.trim_dist = 1, 1, 1, 5.0
+        p.loss_kind, p.loss_metric, p.has_weight, p.save_for_backward = _capi.LOSS_CAUCHY, 1.0, 1, 1
+        p.tolerance, p.tanh_steepness, p.match_ratio_thresh = 1e-5, 5.0, 0.1
+        p.nn_slices, p.nn_backend = args.nn_slices, backend
+        ws_bytes, sv_bytes = lib.mmb_icp_workspace_bytes(p), lib.mmb_icp_saved_bytes(p)
+        bufs = dict(ws=torch.empty(ws_bytes, dtype=torch.uint8, device=dev), sv=torch.empty(sv_bytes, dtype=torch.uint8, device=dev),
+                    T=torch.empty((N, 4, 4), **f32), pc=torch.empty((N, n, 3), **f32), de=torch.zeros((N, K, 6), **f32),
+                    wh=torch.zeros((N, K, n), **f32), co=torch.zeros((N, K), **f32),
+                    cv=torch.zeros(N, dtype=torch.uint8, device=dev), it=torch.zeros(N, **f32), mr=torch.zeros(N, **f32),
+                    idn=torch.zeros(1, dtype=torch.int32, device=dev))
+        ms3, cnt3 = (C.c_float * NC)(), (C.c_int32 * NC)()
+        acc_ms, acc_n = [0.0] * NC, [0] * NC
+        for rep in range(2 + min(args.steps, 5)):
+            flush.fill_(1)
+            rc = lib.mmb_icp_forward_profiled(p, _capi.ptr(d_src), _capi.ptr(d_tgt), _capi.ptr(d_T0), _capi.ptr(w_det),
+                                              _capi.ptr(bufs["T"]), _capi.ptr(bufs["pc"]), _capi.ptr(bufs["de"]),
+                                              _capi.ptr(bufs["wh"]), _capi.ptr(bufs["co"]), _capi.ptr(bufs["cv"]),
+                                              _capi.ptr(bufs["it"]), _capi.ptr(bufs["mr"]), _capi.ptr(bufs["idn"]),
+                                              _capi.ptr(bufs["sv"]), _capi.ptr(bufs["ws"]), ws_bytes, _capi.stream_ptr(),
+                                              ms3, cnt3)
+            _capi.check(rc, "mmb_icp_forward_profiled")
+            if rep >= 2:
+                for c in range(NC):
+                    acc_ms[c] += ms3[c]; acc_n[c] += cnt3[c]
+        reps = max(1, acc_n[0] // K)
+        return dict(nn_ms=acc_ms[0] / max(acc_n[0], 1), step_ms=acc_ms[1] / max(acc_n[1], 1),
+                    fwd_ms=sum(acc_ms) / reps, nn_share=acc_ms[0] / max(sum(acc_ms), 1e-9),
+                    bound_ms=acc_ms[3] / reps, build_ms=acc_ms[4] / reps, other_ms=acc_ms[2] / reps)
+
+    use_grid = NN_BACKENDS[args.nn_backend] == 2 or (NN_BACKENDS[args.nn_backend] == 0 and m >= 8192)
+    prof = profile_forward(NN_BACKENDS[args.nn_backend])
+    prof_brute = profile_forward(1) if use_grid else prof       # the exhaustive kernel, same data, same run
+    nn_ms, step_ms, fwd_ms = prof["nn_ms"], prof["step_ms"], prof["fwd_ms"]
 
     # FP32 pipe rate measured here (no CUDA-core FP32 figure in MEASURED_PEAKS.json)
     probe_out = torch.zeros(4, **f32)
@@ -290,7 +300,7 @@ def run_ours(args, wl, rank, world, local_rank):
         peak["ffma2" if packed else "ffma"] = blocks * 256 * iters * 8 * 2 * (2 if packed else 1) / (best * 1e-3) / 1e12
     peak_tf = max(peak.values())
     nn_flop = FLOP_PER_PAIR * N * n * m
-    achieved_tf = nn_flop / (nn_ms * 1e-3) / 1e12
+    brute_tf = nn_flop / (prof_brute["nn_ms"] * 1e-3) / 1e12
 
     peaks_file = os.path.join(ROOT, "MEASURED_PEAKS.json")
     hbm_peak = json.load(open(peaks_file)).get("hbm_gbs") if os.path.exists(peaks_file) else None
@@ -306,7 +316,36 @@ def run_ours(args, wl, rank, world, local_rank):
         cpu = {"value": pairs / secs, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"{pairs} pair(s) of this workload x {K} it fwd+bwd, fp32, torch.cdist+argmin NN, {secs:.1f} s"}
 
-    launches_per_step = (2 + 2 + 2 * K + 1) + 1              # init, pack, sub-pack, bound pass, K x (nn, step), finish; backward
+    peak_src = ("mmb_fp32_probe in this run (max of FFMA and FFMA2 chains); "
+                "MEASURED_PEAKS.json has no CUDA-core FP32 entry")
+    roofline_brute = {"kernel": "nn_search_kernel (--nn-backend brute)", "bound": "fp32", "achieved": brute_tf,
+                      "peak": peak_tf, "unit": "TFLOP/s", "frac": brute_tf / peak_tf,
+                      "traffic": 42.0e6 if args.workload == "c3" else None, "traffic_source": "profiles/r01b_ncu_c3_summary.md (ncu --set full, c3, per launch)",
+                      "flop_per_launch": nn_flop, "ms_per_launch": prof_brute["nn_ms"], "peak_source": peak_src,
+                      "peak_detail": peak, "share_of_forward": prof_brute["nn_share"], "forward_ms": prof_brute["fwd_ms"]}
+    if use_grid:
+        # cell-grid search: HBM/L2-gather bound.  Algorithmic bytes per launch: per pair
+        # n x (12 B source + 4 B previous index + 12 B result) + m x 16 B sorted copy + the cell table.
+        grid_bytes = N * (n * 28 + m * 16 + (65536 + 8) * 4)
+        hbm = hbm_peak or 6455.9
+        gbs = grid_bytes / (nn_ms * 1e-3) / 1e9
+        roofline = {"kernel": "nn_grid_kernel", "bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s",
+                    "frac": gbs / hbm, "traffic": None, "bytes_per_launch": grid_bytes, "ms_per_launch": nn_ms,
+                    "peak_source": "MEASURED_PEAKS.json hbm_gbs" if hbm_peak else "fallback 6455.9 GB/s",
+                    "work_avoiding": True,
+                    "exhaustive_equivalent_tflops": nn_flop / (nn_ms * 1e-3) / 1e12,
+                    "note": "exact cell-grid search: same indices as the exhaustive kernel with ~1e-3 of its distance "
+                            "evaluations; latency/issue-bound gathers from L2, not at the HBM roofline; "
+                            "roofline_exhaustive_nn is the compute-bound kernel on the same data in the same run",
+                    "share_of_forward": prof["nn_share"], "forward_ms": fwd_ms,
+                    "step_kernel_ms_per_launch": step_ms, "grid_build_ms": prof["build_ms"],
+                    "nn_backend": args.nn_backend}
+    else:
+        roofline = dict(roofline_brute, kernel="nn_search_kernel", step_kernel_ms_per_launch=step_ms,
+                        bound_pass_ms=prof["bound_ms"], nn_backend=args.nn_backend)
+
+    # ours only: brute = init, pack, sub-pack, bound pass; grid = init, geometry, count, scan, scatter
+    launches_per_step = ((5 if use_grid else 4) + 2 * K + 1) + 1      # + K x (nn, step), finish; backward
     h2d = sum(host[k].numel() * 4 for k in host)
     d2h = out_T.numel() * 4 + out_gw.numel() * 4
     line = {
@@ -320,16 +359,8 @@ def run_ours(args, wl, rank, world, local_rank):
         "e2e": {"value": world * N / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches_per_step * args.steps * 2,
-        "roofline": {"kernel": "nn_search_kernel", "bound": "fp32", "achieved": achieved_tf, "peak": peak_tf,
-                     "unit": "TFLOP/s", "frac": achieved_tf / peak_tf, "traffic": None,
-                     "flop_per_launch": nn_flop, "ms_per_launch": nn_ms,
-                     "peak_source": "mmb_fp32_probe in this run (max of FFMA and FFMA2 chains); "
-                                    "MEASURED_PEAKS.json has no CUDA-core FP32 entry",
-                     "peak_detail": peak, "share_of_forward": acc_ms[0] / max(sum(acc_ms), 1e-9),
-                     "forward_ms": fwd_ms, "step_kernel_ms_per_launch": step_ms,
-                     "bound_pass_ms": acc_ms[3] / reps, "grid_build_ms": acc_ms[4] / reps,
-                     "nn_backend": args.nn_backend,
-                     "hbm_gbs_measured_peak": hbm_peak},
+        "roofline": roofline,
+        "roofline_exhaustive_nn": roofline_brute,
         "cpu_baseline": cpu,
         "clocks": clocks,
     }

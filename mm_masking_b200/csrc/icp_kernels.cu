@@ -608,36 +608,46 @@ __global__ void grid_count_kernel(const T* __restrict__ target, int cols, int N,
   }
 }
 
-// exclusive scan of one pair's GRID_CELLS + 1 counts; the counts array becomes the scatter cursor
+// exclusive scan of one pair's GRID_CELLS + 1 counts; the counts array becomes the scatter cursor.
+// One block per pair; warp w owns cells [2048 w, 2048 (w+1)) and walks them 128 at a time with
+// coalesced 16-byte accesses (pass 1: warp totals; pass 2: prefix within the warp's chunk).
 __global__ void __launch_bounds__(1024) grid_scan_kernel(int* __restrict__ counts, int* __restrict__ start) {
-  constexpr int PER = GRID_CELLS / 1024;
+  constexpr int CHUNK = GRID_CELLS / 32;          // cells per warp
+  constexpr int ITER = CHUNK / 128;
   const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  int* cnt = counts + (size_t)b * GRID_STRIDE;
-  int* st = start + (size_t)b * GRID_STRIDE;
+  int4* cnt4 = reinterpret_cast<int4*>(counts + (size_t)b * GRID_STRIDE + warp * CHUNK);
+  int4* st4 = reinterpret_cast<int4*>(start + (size_t)b * GRID_STRIDE + warp * CHUNK);
   __shared__ int wsum[32];
-  int v[PER], sum = 0;
+  int4 v[ITER];
+  int sum = 0;
 #pragma unroll
-  for (int k = 0; k < PER; k += 4) {
-    const int4 q = *reinterpret_cast<const int4*>(cnt + tid * PER + k);
-    v[k] = q.x; v[k + 1] = q.y; v[k + 2] = q.z; v[k + 3] = q.w;
-    sum += q.x + q.y + q.z + q.w;
-  }
-  int inc = sum;
+  for (int i = 0; i < ITER; ++i) { v[i] = cnt4[i * 32 + lane]; sum += v[i].x + v[i].y + v[i].z + v[i].w; }
 #pragma unroll
-  for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
-  if (lane == 31) wsum[warp] = inc;
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  if (lane == 0) wsum[warp] = sum;
   __syncthreads();
   if (warp == 0) {
     int w = wsum[lane];
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += t; }
-    wsum[lane] = w;
+    wsum[lane] = w;                                // inclusive
   }
   __syncthreads();
-  int run = inc - sum + (warp > 0 ? wsum[warp - 1] : 0);
+  int run = warp > 0 ? wsum[warp - 1] : 0;         // first slot of this warp's chunk
 #pragma unroll
-  for (int k = 0; k < PER; ++k) { const int c = v[k]; st[tid * PER + k] = run; cnt[tid * PER + k] = run; run += c; }
+  for (int i = 0; i < ITER; ++i) {
+    const int s4 = v[i].x + v[i].y + v[i].z + v[i].w;
+    int inc = s4;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    int4 r;
+    r.x = run + inc - s4; r.y = r.x + v[i].x; r.z = r.y + v[i].y; r.w = r.z + v[i].z;
+    st4[i * 32 + lane] = r; cnt4[i * 32 + lane] = r;
+    run += __shfl_sync(0xffffffffu, inc, 31);
+  }
   if (tid == 1023) {
+    int* cnt = counts + (size_t)b * GRID_STRIDE;
+    int* st = start + (size_t)b * GRID_STRIDE;
     const int outside = cnt[GRID_OUTSIDE];
     st[GRID_OUTSIDE] = run; cnt[GRID_OUTSIDE] = run; st[GRID_OUTSIDE + 1] = run + outside;
   }
