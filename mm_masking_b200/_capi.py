@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmm_masking_b200.so")
+LIB_PATH = os.environ.get("MMB_LIBRARY") or os.path.join(_HERE, "libmm_masking_b200.so")   # override: A/B builds
 
 F32, F64 = 0, 1
 PT2PL, PT2PT = 0, 1

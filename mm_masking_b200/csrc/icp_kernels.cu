@@ -702,6 +702,15 @@ struct GridNNArgs {
 //     target; that gives D for the square scan (skipped when D is already below the block's cell
 //     size and below the distance to the grid border: nothing outside the block can win or tie).
 constexpr int GRIDNN_WARPS = GRIDNN_THREADS / 32;
+#ifndef MMB_GRID_FILTER
+#define MMB_GRID_FILTER 1
+#endif
+#ifndef MMB_GRID_REDUX
+#define MMB_GRID_REDUX 1
+#endif
+#ifndef MMB_GRID_MINBLOCKS
+#define MMB_GRID_MINBLOCKS 8
+#endif
 constexpr int GRID_SPLIT = 64;
 
 // an upper bound of sqrt(v), v >= 0, within 2^-22 relative (one MUFU instead of the fp64 routine)
@@ -716,7 +725,7 @@ __device__ __forceinline__ int clamp_cell(double v) {
 }
 
 template <typename T, int DIM>
-__global__ void __launch_bounds__(GRIDNN_THREADS) nn_grid_kernel(GridNNArgs a) {
+__global__ void __launch_bounds__(GRIDNN_THREADS, MMB_GRID_MINBLOCKS) nn_grid_kernel(GridNNArgs a) {
   const int b = blockIdx.y;
   if (a.counters && a.counters[1]) return;
   if (a.frozen && a.frozen[b]) return;
@@ -744,14 +753,42 @@ __global__ void __launch_bounds__(GRIDNN_THREADS) nn_grid_kernel(GridNNArgs a) {
   const double abs_slack = 1.0e-9 * (1.0 + fabs(fx) + fabs(fy));
 
   double D2 = 1.0e308; int I = INT_MAX;                    // per-lane partial minimum
+  // fp32 inputs: a conservative fp32 filter in front of the exact comparison.  With q~ = fl32(q)
+  // and the targets exact in fp32, the computed f = fl32(|t - q~|^2) of a target at true distance
+  // d obeys f <= (d + 2^-23 (|q|_1 + 2 d))^2 (1 + 2^-22), so every target with d <= D satisfies
+  // f <= thr(D) below and only those go on to the fp64 comparison.
+  constexpr bool FILTER = MMB_GRID_FILTER && sizeof(T) == 4;
+  const float qxf = (float)qx, qyf = (float)qy, qzf = (float)qz;
+  const double q1 = fabs(qx) + fabs(qy) + (DIM == 3 ? fabs(qz) : 0.0);
+  float thr = __int_as_float(0x7f800000);                  // +inf until a bound is known
+  auto set_thr = [&]() {
+    if (!FILTER) return;
+    double t = sqrt_upper(D2) * (1.0 + 4.76837158203125e-07) + 1.1920928955078125e-07 * q1;
+    t = t * t * (1.0 + 4.76837158203125e-07);
+    thr = __double2float_ru(t);
+  };
   auto scan = [&](int s0, int e0) {
     for (int p = s0 + lane; p < e0; p += 32) {
-      double tx, ty, tz; int j;
-      load_sorted(sorted + p, tx, ty, tz, j);
-      const double dx = tx - qx, dy = ty - qy;
-      double e2 = fma(dy, dy, __dmul_rn(dx, dx));
-      if (DIM == 3) { const double dz = tz - qz; e2 = fma(dz, dz, e2); }
-      if (e2 < D2 || (e2 == D2 && j < I)) { D2 = e2; I = j; }
+      if (FILTER) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(sorted + p));
+        const float dxf = v.x - qxf, dyf = v.y - qyf;
+        float f = fmaf(dyf, dyf, dxf * dxf);
+        if (DIM == 3) { const float dzf = v.z - qzf; f = fmaf(dzf, dzf, f); }
+        if (f <= thr) {
+          const double dx = (double)v.x - qx, dy = (double)v.y - qy;
+          double e2 = fma(dy, dy, __dmul_rn(dx, dx));
+          if (DIM == 3) { const double dz = (double)v.z - qz; e2 = fma(dz, dz, e2); }
+          const int j = __float_as_int(v.w);
+          if (e2 < D2 || (e2 == D2 && j < I)) { D2 = e2; I = j; set_thr(); }
+        }
+      } else {
+        double tx, ty, tz; int j;
+        load_sorted(sorted + p, tx, ty, tz, j);
+        const double dx = tx - qx, dy = ty - qy;
+        double e2 = fma(dy, dy, __dmul_rn(dx, dx));
+        if (DIM == 3) { const double dz = tz - qz; e2 = fma(dz, dz, e2); }
+        if (e2 < D2 || (e2 == D2 && j < I)) { D2 = e2; I = j; }
+      }
     }
   };
   // the cells (x0..x1) x (y0..y1) of level L (at most 3 x 3): lane c fetches the range of cell c,
@@ -795,14 +832,27 @@ __global__ void __launch_bounds__(GRIDNN_THREADS) nn_grid_kernel(GridNNArgs a) {
     }
   };
   auto scan_outside = [&]() { scan(__ldg(start + GRID_OUTSIDE), __ldg(start + GRID_OUTSIDE + 1)); };
-  // lexicographic (D2, I) minimum over the warp, left in every lane
+  // lexicographic (D2, I) minimum over the warp, left in every lane.  D2 >= 0, so its bit pattern
+  // orders like an unsigned integer: three 32-bit warp minima (REDUX) instead of a shuffle tree.
   auto reduce = [&]() {
+#if !MMB_GRID_REDUX
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       const double d = __shfl_xor_sync(0xffffffffu, D2, o);
       const int j = __shfl_xor_sync(0xffffffffu, I, o);
       if (d < D2 || (d == D2 && j < I)) { D2 = d; I = j; }
     }
+    set_thr();
+    return;
+#endif
+    const unsigned long long bits = (unsigned long long)__double_as_longlong(D2);
+    const unsigned hi = (unsigned)(bits >> 32), lo = (unsigned)bits;
+    const unsigned mhi = __reduce_min_sync(0xffffffffu, hi);
+    const unsigned mlo = __reduce_min_sync(0xffffffffu, hi == mhi ? lo : 0xffffffffu);
+    const bool mine = hi == mhi && lo == mlo;
+    I = __reduce_min_sync(0xffffffffu, mine ? I : INT_MAX);
+    D2 = __longlong_as_double((long long)(((unsigned long long)mhi << 32) | mlo));
+    set_thr();
   };
 
   bool done = false;
@@ -810,7 +860,7 @@ __global__ void __launch_bounds__(GRIDNN_THREADS) nn_grid_kernel(GridNNArgs a) {
     const int j0 = a.idx_prev[(size_t)b * a.n + qi];
     if (j0 >= 0 && j0 < a.m) {
       const double d0 = exact_dist2<T, DIM>(tgt + (size_t)j0 * a.cols, qx, qy, qz);
-      if (d0 < 1.0e300) { D2 = d0; I = j0; }
+      if (d0 < 1.0e300) { D2 = d0; I = j0; set_thr(); }
     }
   }
   if (!(D2 < 1.0e300)) {
