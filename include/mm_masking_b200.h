@@ -166,6 +166,34 @@ int mmb_polar_to_cart(int32_t B, int32_t A, int32_t R, int32_t width, int32_t dt
                       const void* range_tab, const void* angle_tab, double radar_res,
                       int32_t interpolate_crossover, int32_t fix_wobble, void* out, void* stream);
 
+/* Adjoint of mmb_polar_to_cart with respect to the scan (what autograd computes through the
+ * `grid_sample` of radar_utils.py:334; the wrap-padded azimuth rows of :317-319 fold back onto rows
+ * A-1 and 0).   grad_out (B,width,width)   grad_scan (B,A,R): ACCUMULATED into, caller zero-fills. */
+int mmb_polar_to_cart_bwd(int32_t B, int32_t A, int32_t R, int32_t width, int32_t dtype,
+                          const void* grad_out, const void* azimuths, const void* range_tab,
+                          const void* angle_tab, double radar_res, int32_t interpolate_crossover,
+                          int32_t fix_wobble, void* grad_scan, void* stream);
+
+/* Cartesian -> polar resampling.  Replaces radar_utils.py:338-372 (`radar_cartesian_to_polar`).
+ * range_tab (R): the range of every polar bin (`form_polar_range_grid` :421-438), from the caller.
+ *   cart (B,H,W)   azimuths (B,A)   out (B,A,R) */
+int mmb_cart_to_polar(int32_t B, int32_t A, int32_t R, int32_t H, int32_t W, int32_t dtype,
+                      double cart_res, const void* cart, const void* azimuths,
+                      const void* range_tab, void* out, void* stream);
+/*   grad_out (B,A,R)   grad_cart (B,H,W): ACCUMULATED into with atomics, caller zero-fills. */
+int mmb_cart_to_polar_bwd(int32_t B, int32_t A, int32_t R, int32_t H, int32_t W, int32_t dtype,
+                          double cart_res, const void* grad_out, const void* azimuths,
+                          const void* range_tab, void* grad_cart, void* stream);
+
+/* Occupancy BEV of a point cloud.  Replaces radar_utils.py:142-165 (`extract_bev_from_pts`): the four
+ * floor/ceil pixels of every point are 1, out-of-range coordinates go to the centre pixel, which
+ * ends as 0.  center_offset: the pixel offset `point_to_cart_idx` adds (320 = its default width / 2,
+ * which the reference uses whatever `cart_pixel_width` is, :144).
+ *   pts (N,n,pt_cols)   bev (N,width,width): fully written (zero-filled here). */
+int mmb_bev_from_points(int32_t N, int32_t n, int32_t pt_cols, int32_t width, int32_t dtype,
+                        double cart_res, double center_offset, const void* pts, void* bev,
+                        void* stream);
+
 /* GO-CFAR mask.  Replaces radar_utils.py:29-69 (`cfar_mask`). */
 typedef struct mmb_cfar_params {
   int32_t B, A, R;         /* scans, azimuths per scan, range bins */

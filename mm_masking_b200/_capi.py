@@ -70,6 +70,10 @@ SIGNATURES = {
     "mmb_sample_weights_fwd": (C.c_int, [C.c_int32] * 6 + [C.c_double, _P, _P, _P, _P]),
     "mmb_sample_weights_bwd": (C.c_int, [C.c_int32] * 6 + [C.c_double, _P, _P, _P, _P]),
     "mmb_polar_to_cart": (C.c_int, [C.c_int32] * 6 + [_P] * 4 + [C.c_double, C.c_int32, C.c_int32, _P, _P]),
+    "mmb_polar_to_cart_bwd": (C.c_int, [C.c_int32] * 5 + [_P] * 4 + [C.c_double, C.c_int32, C.c_int32, _P, _P]),
+    "mmb_cart_to_polar": (C.c_int, [C.c_int32] * 6 + [C.c_double] + [_P] * 5),
+    "mmb_cart_to_polar_bwd": (C.c_int, [C.c_int32] * 6 + [C.c_double] + [_P] * 5),
+    "mmb_bev_from_points": (C.c_int, [C.c_int32] * 5 + [C.c_double, C.c_double, _P, _P, _P]),
     "mmb_cfar_columns": (C.c_int, [C.POINTER(CfarParams)] + [C.POINTER(C.c_int32)] * 3),
     "mmb_cfar_mask": (C.c_int, [C.POINTER(CfarParams), _P, _P, _P]),
     "mmb_extract_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),

@@ -133,12 +133,15 @@ struct PolarArgs {
   const void* azimuths;          // (B,A) working dtype
   const void* range_tab; const void* angle_tab;   // (width*width)
   void* out;                     // (B,width,width)
+  const void* grad_out; void* grad_scan;           // adjoint: (B,width,width) in, (B,A,R) accumulated
   int B, A, R, width;
   int interpolate_crossover, fix_wobble;
   double radar_res;
 };
 
-template <typename T>
+// BWD = true: the adjoint with respect to the scan (what autograd does for the grid_sample of
+// radar_utils.py:334): the same taps, grad_out[pixel] * weight accumulated into grad_scan.
+template <typename T, bool BWD>
 __global__ void __launch_bounds__(ROW_THREADS) polar_to_cart_kernel(PolarArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   T* saz = reinterpret_cast<T*>(smem_raw);
@@ -188,6 +191,18 @@ __global__ void __launch_bounds__(ROW_THREADS) polar_to_cart_kernel(PolarArgs a)
   const T gy = add_rn(mul_rn(div_rn(v, (T)(H - 1)), (T)2), (T)-1);           // :323
   const Taps<T> t = bilinear_taps<T>(gx, gy, a.R, H);
 
+  if (BWD) {
+    const T go = static_cast<const T*>(a.grad_out)[(size_t)b * npix + pix];
+    T* gs = static_cast<T*>(a.grad_scan) + (size_t)b * a.A * a.R;
+    auto put = [&](int x, int y, T w) {
+      if (!inside(x, y, a.R, H)) return;
+      int r = y;
+      if (a.interpolate_crossover) r = y == 0 ? a.A - 1 : (y == a.A + 1 ? 0 : y - 1);
+      atomicAdd(gs + (size_t)r * a.R + x, mul_rn(go, w));
+    };
+    put(t.x0, t.y0, t.nw); put(t.x0 + 1, t.y0, t.ne); put(t.x0, t.y0 + 1, t.sw); put(t.x0 + 1, t.y0 + 1, t.se);
+    return;
+  }
   Scan<T> sc; sc.base = a.scan; sc.kind = a.scan_kind; sc.row_stride = a.scan_row_stride;
   const size_t row0 = (size_t)b * a.A;
   auto fetch = [&](int x, int y) -> T {
@@ -630,6 +645,90 @@ static int fill_peak(const mmb_extract_params* p, const void* src, PeakArgs& a) 
   return MMB_OK;
 }
 
+// ---------------------------------------------------------------------------------------------
+// N2: occupancy BEV of a point cloud (radar_utils.py:142-165, `extract_bev_from_pts`)
+// ---------------------------------------------------------------------------------------------
+// idx = (-x / res + half, y / res + half) (point_to_cart_idx, :374-397; half = 320, its DEFAULT width / 2,
+// whatever W is, :144); a coordinate < 0 or > W-1
+// is replaced by W//2 (:147-148, per coordinate); the four floor/ceil pixels get 1 (:156-159); the
+// centre pixel, which collects the out-of-range and padding points, ends as 0 (:163).  Writes are
+// idempotent, so no atomics; the caller zero-fills `bev`.
+template <typename T>
+__global__ void bev_from_points_kernel(const T* __restrict__ pts, int pt_cols, int N, int n, int W, T cart_res,
+                                       T half, T* __restrict__ bev) {
+  const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (size_t)N * n) return;
+  const int b = (int)(g / n);
+  const T* p = pts + g * pt_cols;
+  T u = add_rn(div_rn(-p[0], cart_res), half), v = add_rn(div_rn(p[1], cart_res), half);
+  const T mid = (T)(W / 2);
+  if (u < (T)0) u = mid;
+  if (u > (T)(W - 1)) u = mid;
+  if (v < (T)0) v = mid;
+  if (v > (T)(W - 1)) v = mid;
+  if (!(u >= (T)0 && u <= (T)(W - 1) && v >= (T)0 && v <= (T)(W - 1))) return;      // NaN coordinates
+  const int uf = (int)t_floor(u), uc = (int)ceil((double)u), vf = (int)t_floor(v), vc = (int)ceil((double)v);
+  T* img = bev + (size_t)b * W * W;
+  const int c = W / 2;
+  auto put = [&](int r, int col) { if (!(r == c && col == c)) img[(size_t)r * W + col] = (T)1; };
+  put(uc, vf); put(uc, vc); put(uf, vf); put(uf, vc);
+}
+
+// ---------------------------------------------------------------------------------------------
+// N3: Cartesian -> polar resampling (radar_utils.py:338-372, `radar_cartesian_to_polar`) + adjoint
+// ---------------------------------------------------------------------------------------------
+// Output pixel (azimuth i, range bin j) samples the Cartesian image at X = sin(az_i) r_j,
+// Y = cos(az_i) r_j: u = X / res, v = -Y / res, normalised by (W-1)/2 resp. (H-1)/2, bilinear,
+// zeros outside, align_corners.  r_j comes from the caller (`torch.linspace`, form_polar_range_grid
+// :421-438).  One block per (range segment, azimuth, scan); sin/cos once per block.
+struct CartPolarArgs {
+  const void* cart;              // (B,H,W)
+  const void* azimuths;          // (B,A)
+  const void* range_tab;         // (R)
+  void* out;                     // (B,A,R)
+  const void* grad_out; void* grad_cart;
+  int B, A, R, H, W;
+  double cart_res;
+};
+
+template <typename T, bool BWD>
+__global__ void __launch_bounds__(ROW_THREADS) cart_to_polar_kernel(CartPolarArgs a) {
+  const int i = blockIdx.y, b = blockIdx.z;
+  __shared__ T s_sc[2];
+  if (threadIdx.x == 0) {
+    const T az = static_cast<const T*>(a.azimuths)[(size_t)b * a.A + i];
+    s_sc[0] = (T)sin((double)az); s_sc[1] = (T)cos((double)az);
+    if (sizeof(T) == 4) { s_sc[0] = (T)sinf((float)az); s_sc[1] = (T)cosf((float)az); }
+  }
+  __syncthreads();
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= a.R) return;
+  const T r = static_cast<const T*>(a.range_tab)[j];
+  const T X = mul_rn(s_sc[0], r), Y = mul_rn(s_sc[1], r);                       // :347-348
+  const T res = (T)a.cart_res;
+  T u = div_rn(X, res), v = div_rn(-Y, res);                                   // :354-355
+  u = mul_rn(div_rn(u, (T)(a.W - 1)), (T)2);                                   // :358-359
+  v = mul_rn(div_rn(v, (T)(a.H - 1)), (T)2);
+  const Taps<T> t = bilinear_taps<T>(u, v, a.W, a.H);
+  const size_t o = ((size_t)b * a.A + i) * a.R + j;
+  if (BWD) {
+    const T go = static_cast<const T*>(a.grad_out)[o];
+    T* gc = static_cast<T*>(a.grad_cart) + (size_t)b * a.H * a.W;
+    if (inside(t.x0, t.y0, a.W, a.H)) atomicAdd(gc + (size_t)t.y0 * a.W + t.x0, mul_rn(go, t.nw));
+    if (inside(t.x0 + 1, t.y0, a.W, a.H)) atomicAdd(gc + (size_t)t.y0 * a.W + t.x0 + 1, mul_rn(go, t.ne));
+    if (inside(t.x0, t.y0 + 1, a.W, a.H)) atomicAdd(gc + (size_t)(t.y0 + 1) * a.W + t.x0, mul_rn(go, t.sw));
+    if (inside(t.x0 + 1, t.y0 + 1, a.W, a.H)) atomicAdd(gc + (size_t)(t.y0 + 1) * a.W + t.x0 + 1, mul_rn(go, t.se));
+    return;
+  }
+  const T* img = static_cast<const T*>(a.cart) + (size_t)b * a.H * a.W;
+  T acc = (T)0;
+  if (inside(t.x0, t.y0, a.W, a.H)) acc = mul_rn(img[(size_t)t.y0 * a.W + t.x0], t.nw);
+  if (inside(t.x0 + 1, t.y0, a.W, a.H)) acc = add_rn(acc, mul_rn(img[(size_t)t.y0 * a.W + t.x0 + 1], t.ne));
+  if (inside(t.x0, t.y0 + 1, a.W, a.H)) acc = add_rn(acc, mul_rn(img[(size_t)(t.y0 + 1) * a.W + t.x0], t.sw));
+  if (inside(t.x0 + 1, t.y0 + 1, a.W, a.H)) acc = add_rn(acc, mul_rn(img[(size_t)(t.y0 + 1) * a.W + t.x0 + 1], t.se));
+  static_cast<T*>(a.out)[o] = acc;
+}
+
 }  // namespace mmb
 
 using namespace mmb;
@@ -682,6 +781,7 @@ int mmb_polar_to_cart(int32_t B, int32_t A, int32_t R, int32_t width, int32_t dt
   a.scan = scan; a.scan_kind = scan_kind_of(dtype, scan_u8);
   a.scan_row_stride = scan_u8 ? (size_t)R + 11 : (size_t)R; a.scan_batch_stride = 0;
   a.azimuths = azimuths; a.range_tab = range_tab; a.angle_tab = angle_tab; a.out = out;
+  a.grad_out = nullptr; a.grad_scan = nullptr;
   a.B = B; a.A = A; a.R = R; a.width = width;
   a.interpolate_crossover = interpolate_crossover ? 1 : 0; a.fix_wobble = fix_wobble ? 1 : 0;
   a.radar_res = radar_res;
@@ -691,12 +791,12 @@ int mmb_polar_to_cart(int32_t B, int32_t A, int32_t R, int32_t width, int32_t dt
   int rc;
   if (dtype == MMB_F32) {
     const size_t smem = (size_t)A * sizeof(float);
-    if ((rc = opt_in_smem(polar_to_cart_kernel<float>, smem))) return rc;
-    polar_to_cart_kernel<float><<<grid, ROW_THREADS, smem, st>>>(a);
+    if ((rc = opt_in_smem(polar_to_cart_kernel<float, false>, smem))) return rc;
+    polar_to_cart_kernel<float, false><<<grid, ROW_THREADS, smem, st>>>(a);
   } else {
     const size_t smem = (size_t)A * sizeof(double);
-    if ((rc = opt_in_smem(polar_to_cart_kernel<double>, smem))) return rc;
-    polar_to_cart_kernel<double><<<grid, ROW_THREADS, smem, st>>>(a);
+    if ((rc = opt_in_smem(polar_to_cart_kernel<double, false>, smem))) return rc;
+    polar_to_cart_kernel<double, false><<<grid, ROW_THREADS, smem, st>>>(a);
   }
   return check_launch();
 }
@@ -862,6 +962,89 @@ int mmb_kstrong_write(const mmb_kstrong_params* p, const void* azimuths, void* w
                                                         p->range_offset, out_cap, static_cast<double*>(points_out),
                                                         rows_out, bins_out);
   return check_launch();
+}
+
+int mmb_polar_to_cart_bwd(int32_t B, int32_t A, int32_t R, int32_t width, int32_t dtype, const void* grad_out,
+                          const void* azimuths, const void* range_tab, const void* angle_tab, double radar_res,
+                          int32_t interpolate_crossover, int32_t fix_wobble, void* grad_scan, void* stream) {
+  if (B <= 0 || A <= 1 || R <= 1 || width <= 0) return MMB_ERR_INVALID_SHAPE;
+  if (dtype != MMB_F32 && dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  if (!grad_out || !azimuths || !range_tab || !angle_tab || !grad_scan) return MMB_ERR_NULL_POINTER;
+  PolarArgs a;
+  a.scan = nullptr; a.scan_kind = IN_F32; a.scan_row_stride = (size_t)R; a.scan_batch_stride = 0;
+  a.azimuths = azimuths; a.range_tab = range_tab; a.angle_tab = angle_tab; a.out = nullptr;
+  a.grad_out = grad_out; a.grad_scan = grad_scan;
+  a.B = B; a.A = A; a.R = R; a.width = width;
+  a.interpolate_crossover = interpolate_crossover ? 1 : 0; a.fix_wobble = fix_wobble ? 1 : 0;
+  a.radar_res = radar_res;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int tiles = (width + 15) / 16;
+  dim3 grid(tiles * tiles, B);
+  int rc;
+  if (dtype == MMB_F32) {
+    const size_t smem = (size_t)A * sizeof(float);
+    if ((rc = opt_in_smem(polar_to_cart_kernel<float, true>, smem))) return rc;
+    polar_to_cart_kernel<float, true><<<grid, ROW_THREADS, smem, st>>>(a);
+  } else {
+    const size_t smem = (size_t)A * sizeof(double);
+    if ((rc = opt_in_smem(polar_to_cart_kernel<double, true>, smem))) return rc;
+    polar_to_cart_kernel<double, true><<<grid, ROW_THREADS, smem, st>>>(a);
+  }
+  return check_launch();
+}
+
+int mmb_bev_from_points(int32_t N, int32_t n, int32_t pt_cols, int32_t width, int32_t dtype, double cart_res,
+                        double center_offset, const void* pts, void* bev, void* stream) {
+  if (N <= 0 || n <= 0 || pt_cols < 2 || width <= 0) return MMB_ERR_INVALID_SHAPE;
+  if (dtype != MMB_F32 && dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  if (!pts || !bev) return MMB_ERR_NULL_POINTER;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t esz = dtype == MMB_F32 ? 4 : 8;
+  if (cudaMemsetAsync(bev, 0, (size_t)N * width * width * esz, st) != cudaSuccess) return check_launch();
+  const size_t total = (size_t)N * n;
+  const int blocks = (int)((total + 255) / 256);
+  if (dtype == MMB_F32)
+    bev_from_points_kernel<float><<<blocks, 256, 0, st>>>(static_cast<const float*>(pts), pt_cols, N, n, width,
+                                                          (float)cart_res, (float)center_offset, static_cast<float*>(bev));
+  else
+    bev_from_points_kernel<double><<<blocks, 256, 0, st>>>(static_cast<const double*>(pts), pt_cols, N, n, width,
+                                                           cart_res, center_offset, static_cast<double*>(bev));
+  return check_launch();
+}
+
+static int cart_polar_launch(int bwd, int32_t B, int32_t A, int32_t R, int32_t H, int32_t W, int32_t dtype,
+                             double cart_res, const void* cart, const void* azimuths, const void* range_tab, void* out,
+                             const void* grad_out, void* grad_cart, void* stream) {
+  if (B <= 0 || A <= 0 || R <= 0 || H <= 1 || W <= 1) return MMB_ERR_INVALID_SHAPE;
+  if (dtype != MMB_F32 && dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  if (!azimuths || !range_tab) return MMB_ERR_NULL_POINTER;
+  if (bwd ? (!grad_out || !grad_cart) : (!cart || !out)) return MMB_ERR_NULL_POINTER;
+  CartPolarArgs a;
+  a.cart = cart; a.azimuths = azimuths; a.range_tab = range_tab; a.out = out;
+  a.grad_out = grad_out; a.grad_cart = grad_cart;
+  a.B = B; a.A = A; a.R = R; a.H = H; a.W = W; a.cart_res = cart_res;
+  dim3 grid((R + ROW_THREADS - 1) / ROW_THREADS, A, B);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == MMB_F32) {
+    if (bwd) cart_to_polar_kernel<float, true><<<grid, ROW_THREADS, 0, st>>>(a);
+    else cart_to_polar_kernel<float, false><<<grid, ROW_THREADS, 0, st>>>(a);
+  } else {
+    if (bwd) cart_to_polar_kernel<double, true><<<grid, ROW_THREADS, 0, st>>>(a);
+    else cart_to_polar_kernel<double, false><<<grid, ROW_THREADS, 0, st>>>(a);
+  }
+  return check_launch();
+}
+
+int mmb_cart_to_polar(int32_t B, int32_t A, int32_t R, int32_t H, int32_t W, int32_t dtype, double cart_res,
+                      const void* cart, const void* azimuths, const void* range_tab, void* out, void* stream) {
+  return cart_polar_launch(0, B, A, R, H, W, dtype, cart_res, cart, azimuths, range_tab, out, nullptr, nullptr, stream);
+}
+
+int mmb_cart_to_polar_bwd(int32_t B, int32_t A, int32_t R, int32_t H, int32_t W, int32_t dtype, double cart_res,
+                          const void* grad_out, const void* azimuths, const void* range_tab, void* grad_cart,
+                          void* stream) {
+  return cart_polar_launch(1, B, A, R, H, W, dtype, cart_res, nullptr, azimuths, range_tab, nullptr, grad_out, grad_cart,
+                           stream);
 }
 
 }  // extern "C"

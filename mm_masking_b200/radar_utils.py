@@ -298,22 +298,131 @@ def extract_weights(mask, scan_pc):
 # ---------------------------------------------------------------------------------------------
 # K1: polar -> Cartesian
 # ---------------------------------------------------------------------------------------------
+class _PolarToCart(torch.autograd.Function):
+    """scan (B,A,R) float (or raw uint8 rows) -> (B,width,width); gradient flows to a float scan."""
+
+    @staticmethod
+    def forward(ctx, x, az, rng, ang, meta):
+        lib = _capi.load_library()
+        dt, u8, B, A, R, width, res, cross, wobble = meta
+        with torch.cuda.device(x.device):
+            out = torch.empty((B, width, width), dtype=az.dtype, device=x.device)
+            _capi.check(lib.mmb_polar_to_cart(B, A, R, width, dt, int(u8), _capi.ptr(x), _capi.ptr(az),
+                                              _capi.ptr(rng), _capi.ptr(ang), res, cross, wobble, _capi.ptr(out),
+                                              _capi.stream_ptr()), "mmb_polar_to_cart")
+        ctx.save_for_backward(az, rng, ang)
+        ctx.meta = meta
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        lib = _capi.load_library()
+        az, rng, ang = ctx.saved_tensors
+        dt, u8, B, A, R, width, res, cross, wobble = ctx.meta
+        if u8:
+            return None, None, None, None, None
+        g = g.contiguous()
+        with torch.cuda.device(g.device):
+            gs = torch.zeros((B, A, R), dtype=g.dtype, device=g.device)
+            _capi.check(lib.mmb_polar_to_cart_bwd(B, A, R, width, dt, _capi.ptr(g), _capi.ptr(az), _capi.ptr(rng),
+                                                  _capi.ptr(ang), res, cross, wobble, _capi.ptr(gs),
+                                                  _capi.stream_ptr()), "mmb_polar_to_cart_bwd")
+        return gs, None, None, None, None
+
+
 def radar_polar_to_cartesian_diff(fft_data, azimuths, radar_resolution, cart_resolution=0.2384, cart_pixel_width=640,
                                   interpolate_crossover=True, fix_wobble=True):
     """Polar scan batch (B,A,R) -> Cartesian (B,width,width), same contract as `radar_utils.py:258-336`
     (including its use of the DEFAULT Cartesian resolution for the pixel grid whatever
     `cart_resolution` is passed, `:276`).  fft_data may also be (B,A,R+11) uint8 raw Navtech rows.
-    Forward only in this round (the reference is differentiable in fft_data)."""
-    lib = _capi.load_library()
-    x, dt, u8, B, A, R = _scan_args(fft_data)
+    Differentiable in a float fft_data, like the reference (autograd through its `grid_sample`)."""
+    assert fft_data.ndim == 3, "raw_scans must be 3D"
+    dev = _device_of(fft_data)
+    x = fft_data.to(dev).contiguous()
+    if x.dtype == torch.uint8:
+        dt, u8, B, A, R = _capi.F32, True, x.shape[0], x.shape[1], x.shape[2] - 11
+    else:
+        _check_dtype(x, "fft_data")
+        dt, u8, B, A, R = _DT[x.dtype], False, x.shape[0], x.shape[1], x.shape[2]
     wdt = torch.float32 if dt == _capi.F32 else torch.float64
-    dev = x.device
     az = azimuths.detach().to(device=dev, dtype=wdt).contiguous()
     rng, ang = form_cart_range_angle_grid(cart_pixel_width=cart_pixel_width, dtype=wdt, device=dev)
-    with torch.cuda.device(dev):
-        out = torch.empty((B, cart_pixel_width, cart_pixel_width), dtype=wdt, device=dev)
-        _capi.check(lib.mmb_polar_to_cart(B, A, R, cart_pixel_width, dt, int(u8), _capi.ptr(x), _capi.ptr(az),
-                                          _capi.ptr(rng), _capi.ptr(ang), float(radar_resolution),
-                                          int(bool(interpolate_crossover)), int(bool(fix_wobble)), _capi.ptr(out),
-                                          _capi.stream_ptr()), "mmb_polar_to_cart")
+    meta = (dt, u8, B, A, R, int(cart_pixel_width), float(radar_resolution), int(bool(interpolate_crossover)),
+            int(bool(fix_wobble)))
+    out = _PolarToCart.apply(x, az, rng, ang, meta)
     return out if fft_data.is_cuda else out.to(fft_data.device)
+
+
+# ---------------------------------------------------------------------------------------------
+# N3: Cartesian -> polar
+# ---------------------------------------------------------------------------------------------
+def form_polar_range_grid(polar_resolution=0.2384, polar_pixel_shape=(400, 3360), dtype=None, device='cpu'):
+    """`radar_utils.py:421-438`: range (m) of every polar pixel, one identical row per azimuth."""
+    polar_range = (polar_pixel_shape[1] - 1) * polar_resolution
+    kw = {} if dtype is None else {"dtype": dtype}
+    range_coords = torch.linspace(0.0, polar_range, polar_pixel_shape[1], **kw).to(device)
+    return range_coords.unsqueeze(0).expand(polar_pixel_shape[0], -1)
+
+
+class _CartToPolar(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, cart, az, rng, cart_res):
+        lib = _capi.load_library()
+        B, H, W = cart.shape
+        A, R = az.shape[1], rng.shape[0]
+        c = cart.detach().contiguous()
+        with torch.cuda.device(c.device):
+            out = torch.empty((B, A, R), dtype=c.dtype, device=c.device)
+            _capi.check(lib.mmb_cart_to_polar(B, A, R, H, W, _DT[c.dtype], cart_res, _capi.ptr(c), _capi.ptr(az),
+                                              _capi.ptr(rng), _capi.ptr(out), _capi.stream_ptr()), "mmb_cart_to_polar")
+        ctx.save_for_backward(az, rng)
+        ctx.meta = (B, A, R, H, W, cart_res)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        lib = _capi.load_library()
+        az, rng = ctx.saved_tensors
+        B, A, R, H, W, cart_res = ctx.meta
+        g = g.contiguous()
+        with torch.cuda.device(g.device):
+            gc = torch.zeros((B, H, W), dtype=g.dtype, device=g.device)
+            _capi.check(lib.mmb_cart_to_polar_bwd(B, A, R, H, W, _DT[g.dtype], cart_res, _capi.ptr(g), _capi.ptr(az),
+                                                  _capi.ptr(rng), _capi.ptr(gc), _capi.stream_ptr()),
+                        "mmb_cart_to_polar_bwd")
+        return gc, None, None, None
+
+
+def radar_cartesian_to_polar(cart, azimuths, radar_resolution, cart_resolution=0.2384, polar_pixel_shape=(400, 3360)):
+    """Cartesian image batch (B,H,W) -> polar (B,A,R), same contract as `radar_utils.py:338-372`,
+    differentiable in `cart`.  The reference casts its sampling grid to float64 (`:370`), so it only
+    runs for float64 images; float32 images are accepted here as well (all-float32 arithmetic)."""
+    _check_dtype(cart, "cart")
+    dev = _device_of(cart)
+    c = cart.to(dev)
+    az = azimuths.detach().to(device=dev, dtype=c.dtype).contiguous()
+    assert c.ndim == 3 and az.ndim == 2 and az.shape[0] == c.shape[0]
+    assert az.shape[1] == polar_pixel_shape[0]
+    rng = form_polar_range_grid(radar_resolution, polar_pixel_shape, dtype=c.dtype, device=dev)[0].contiguous()
+    out = _CartToPolar.apply(c, az, rng, float(cart_resolution))
+    return out if cart.is_cuda else out.to(cart.device)
+
+
+# ---------------------------------------------------------------------------------------------
+# N2: occupancy BEV of a point cloud
+# ---------------------------------------------------------------------------------------------
+def extract_bev_from_pts(pc, cart_pixel_width=640):
+    """Point clouds (N,n,2|3) -> occupancy images (N,width,width), same contract as
+    `radar_utils.py:142-165` (the BCE mask-loss target of `train_icp_weights.py:225`): the four
+    floor/ceil pixels around every point are 1; out-of-range coordinates and padding points fall on
+    the centre pixel, which is zeroed.  Not differentiable (index assignment in the reference)."""
+    _check_dtype(pc, "pc")
+    lib = _capi.load_library()
+    dev = _device_of(pc)
+    pts = pc.detach().to(dev).contiguous()
+    N, n, cols = pts.shape
+    with torch.cuda.device(dev):
+        bev = torch.empty((N, cart_pixel_width, cart_pixel_width), dtype=pts.dtype, device=dev)
+        _capi.check(lib.mmb_bev_from_points(N, n, cols, int(cart_pixel_width), _DT[pts.dtype], 0.2384, 320.0, _capi.ptr(pts),
+                                            _capi.ptr(bev), _capi.stream_ptr()), "mmb_bev_from_points")
+    return bev if pc.is_cuda else bev.to(pc.device)

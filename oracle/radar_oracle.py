@@ -248,6 +248,126 @@ def polar_to_cartesian(fft: np.ndarray, azimuths: np.ndarray, radar_resolution: 
     return out
 
 
+def grid_sample_bilinear_adjoint(grad: np.ndarray, shape, gx: np.ndarray, gy: np.ndarray) -> np.ndarray:
+    """Adjoint of `grid_sample_bilinear` with respect to the image: scatter-add of grad * tap weight
+    into a float64 (H,W) image (what autograd does for `F.grid_sample`)."""
+    dt = grad.dtype.type
+    H, W = shape
+    ix = (gx.astype(grad.dtype) + dt(1)) * dt((W - 1) / 2)
+    iy = (gy.astype(grad.dtype) + dt(1)) * dt((H - 1) / 2)
+    x0 = np.floor(ix); y0 = np.floor(iy)
+    wx1 = ix - x0; wy1 = iy - y0
+    out = np.zeros((H, W), dtype=np.float64)
+    for dy, wy in ((0, dt(1) - wy1), (1, wy1)):
+        for dx, wx in ((0, dt(1) - wx1), (1, wx1)):
+            xi = x0 + dx; yi = y0 + dy
+            ok = (xi >= 0) & (xi <= W - 1) & (yi >= 0) & (yi <= H - 1)
+            np.add.at(out, (yi[ok].astype(np.int64), xi[ok].astype(np.int64)),
+                      (wx * wy)[ok].astype(np.float64) * grad[ok].astype(np.float64))
+    return out
+
+
+def _polar_grid(fft_dtype, az_b, A, R, radar_resolution, cart_pixel_width, interpolate_crossover, fix_wobble):
+    """normalised sampling grid (gx, gy) of `radar_utils.py:283-323` for one scan, and the padded height"""
+    dt = fft_dtype.type
+    rng, ang = form_cart_range_angle_grid(cart_pixel_width=cart_pixel_width, dtype=fft_dtype)
+    u = (rng - dt(radar_resolution / 2)) / dt(radar_resolution)
+    step = (az_b[-1] - az_b[0]) / dt(A - 1)
+    v = (ang - az_b[0]) / step
+    if fix_wobble:
+        c3 = np.searchsorted(az_b, ang.reshape(-1), side='left').reshape(ang.shape)
+        c3[c3 == A] -= 1
+        c2 = c3 - 1
+        c2[c2 < 0] += 1
+        a3 = az_b[c3]; a2 = az_b[c2]
+        diff = ang - a3
+        delta = diff * (diff < 0).astype(fft_dtype) * (c3 > 0).astype(fft_dtype) / (a3 - a2 + dt(1e-14))
+        v = (c3.astype(fft_dtype) + delta).astype(fft_dtype)
+    u = np.where(u < 0, dt(0), u)
+    H = A + 2 if interpolate_crossover else A
+    if interpolate_crossover:
+        v = v + dt(1)
+    return u / dt(R - 1) * dt(2) - dt(1), v / dt(H - 1) * dt(2) - dt(1), H
+
+
+def polar_to_cartesian_backward(grad_out: np.ndarray, azimuths: np.ndarray, R: int, radar_resolution: float,
+                                interpolate_crossover=True, fix_wobble=True) -> np.ndarray:
+    """d(sum grad_out * cart)/d fft for `polar_to_cartesian`: (B,A,R) float64; the wrap-padded rows
+    of `radar_utils.py:317-319` fold back onto rows A-1 and 0."""
+    B, width, _ = grad_out.shape
+    A = azimuths.shape[1]
+    az = azimuths.astype(grad_out.dtype)
+    out = np.zeros((B, A, R), dtype=np.float64)
+    for b in range(B):
+        gx, gy, H = _polar_grid(grad_out.dtype, az[b], A, R, radar_resolution, width, interpolate_crossover, fix_wobble)
+        g = grid_sample_bilinear_adjoint(grad_out[b], (H, R), gx, gy)
+        if interpolate_crossover:
+            out[b] = g[1:-1]
+            out[b, -1] += g[0]
+            out[b, 0] += g[-1]
+        else:
+            out[b] = g
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# N3: Cartesian -> polar (`radar_utils.py:338-372`) and N2: occupancy BEV (`:142-165`)
+# ---------------------------------------------------------------------------------------------
+def _cart_polar_grid(dtype, az_b, radar_resolution, cart_resolution, R, H, W):
+    import torch
+    dt = dtype.type
+    tdt = torch.float32 if dtype == np.float32 else torch.float64
+    rng = torch.linspace(0.0, (R - 1) * radar_resolution, R, dtype=tdt).numpy()      # form_polar_range_grid :421-438
+    X = np.sin(az_b)[:, None] * rng[None, :]
+    Y = np.cos(az_b)[:, None] * rng[None, :]
+    u = X / dt(cart_resolution); v = -Y / dt(cart_resolution)
+    return u / dt(W - 1) * dt(2), v / dt(H - 1) * dt(2)
+
+
+def cartesian_to_polar(cart: np.ndarray, azimuths: np.ndarray, radar_resolution: float, cart_resolution=CART_RES,
+                       polar_pixel_shape=(400, 3360)) -> np.ndarray:
+    """`radar_utils.py:338-372` for a (B,H,W) batch -> (B,A,R)."""
+    B, H, W = cart.shape
+    A, R = polar_pixel_shape
+    az = azimuths.astype(cart.dtype)
+    out = np.zeros((B, A, R), dtype=cart.dtype)
+    for b in range(B):
+        gx, gy = _cart_polar_grid(cart.dtype, az[b], radar_resolution, cart_resolution, R, H, W)
+        out[b] = grid_sample_bilinear(cart[b], gx, gy)
+    return out
+
+
+def cartesian_to_polar_backward(grad_out: np.ndarray, azimuths: np.ndarray, radar_resolution: float, shape,
+                                cart_resolution=CART_RES) -> np.ndarray:
+    """d(sum grad_out * polar)/d cart, float64 (B,H,W)."""
+    B, A, R = grad_out.shape
+    H, W = shape
+    az = azimuths.astype(grad_out.dtype)
+    out = np.zeros((B, H, W), dtype=np.float64)
+    for b in range(B):
+        gx, gy = _cart_polar_grid(grad_out.dtype, az[b], radar_resolution, cart_resolution, R, H, W)
+        out[b] = grid_sample_bilinear_adjoint(grad_out[b], (H, W), gx, gy)
+    return out
+
+
+def extract_bev_from_pts(pc: np.ndarray, cart_pixel_width=640) -> np.ndarray:
+    """`radar_utils.py:142-165`: (N,n,2|3) points -> (N,W,W) occupancy.  `point_to_cart_idx` is called
+    with its DEFAULT width (640) whatever `cart_pixel_width` is (`:144`)."""
+    W = cart_pixel_width
+    idx = point_to_cart_idx(pc)                       # default width: centre offset 320
+    idx = np.where(idx < 0, pc.dtype.type(W // 2), idx)
+    idx = np.where(idx > (W - 1), pc.dtype.type(W // 2), idx)
+    lo = np.floor(idx).astype(np.int64); hi = np.ceil(idx).astype(np.int64)
+    bev = np.zeros((pc.shape[0], W, W), dtype=pc.dtype)
+    rows = np.arange(pc.shape[0])[:, None]
+    bev[rows, hi[:, :, 0], lo[:, :, 1]] = 1
+    bev[rows, hi[:, :, 0], hi[:, :, 1]] = 1
+    bev[rows, lo[:, :, 0], lo[:, :, 1]] = 1
+    bev[rows, lo[:, :, 0], hi[:, :, 1]] = 1
+    bev[:, W // 2, W // 2] = 0
+    return bev
+
+
 # ---------------------------------------------------------------------------------------------
 # K-strongest (C++ specification only)
 # ---------------------------------------------------------------------------------------------
