@@ -210,3 +210,40 @@ def make_radar_scans(B: int, seed: int = 0, n_az: int = 400, n_bins: int = 3360)
     azimuths = (enc.astype(np.float64) * (2 * np.pi / ENCODER_TICKS)).astype(np.float32)
     stamps = raw[:, :, 0:8].copy().view(np.int64).reshape(B, n_az) * 1000
     return dict(raw=raw, fft=fft, azimuths=azimuths, timestamps=stamps)
+
+
+def make_training_batch(N: int, n: int = 2000, m: int = 50000, seed: int = 0, width: int = CART_WIDTH) -> dict:
+    """One training batch in the reference's layout (`icp_weight_dataset.py:357-362`):
+
+        {'loc_data': {'fft_data' (N,W,W), 'fft_cfar' (N,W,W), 'raw_pc' (N,n,3), 'filtered_pc' (N,n,3)},
+         'map_data': {'pc' (N,m,6)}, 'transforms': {'T_ml_init' (N,4,4), 'T_ml_gt' (N,4,4)}}
+
+    as float32 torch tensors on the host.  Points, map and poses come from `make_icp_batch`; the
+    Cartesian radar image is the scan rasterised over an exponential noise floor and the CFAR image
+    its thresholded version (the reference stores both pre-resampled, `icp_weight_dataset.py:83`)."""
+    import torch
+    b = make_icp_batch(N, n, m, seed=seed)
+    rng = np.random.default_rng(seed + 1000)
+    fft = rng.exponential(0.04, (N, width, width)).astype(np.float32)
+    cfar = np.zeros((N, width, width), np.float32)
+    for k in range(N):
+        p = b["source"][k]
+        real = (p[:, 0] != 0) | (p[:, 1] != 0)
+        u = np.clip(np.round(-p[real, 0] / CART_RES + (width - 1) / 2).astype(int), 0, width - 1)
+        v = np.clip(np.round(p[real, 1] / CART_RES + (width - 1) / 2).astype(int), 0, width - 1)
+        fft[k, u, v] += rng.uniform(0.3, 1.0, len(u)).astype(np.float32)
+        cfar[k, u, v] = 1.0
+    fft = np.clip(fft, 0.0, 1.0)
+    t = torch.from_numpy
+    return {"loc_data": {"fft_data": t(fft), "fft_cfar": t(cfar), "raw_pc": t(b["source"].copy()),
+                         "filtered_pc": t(b["source"].copy())},
+            "map_data": {"pc": t(b["target"])},
+            "transforms": {"T_ml_init": t(b["T_init"]), "T_ml_gt": t(b["T_gt"])}}
+
+
+def shard_training_batch(batch: dict, world_size: int, rank: int) -> dict:
+    """this rank's contiguous share of every tensor of a `make_training_batch` dict"""
+    from .dist import shard_range
+    n = batch["transforms"]["T_ml_init"].shape[0]
+    s, e = shard_range(n, world_size, rank)
+    return {k: {kk: vv[s:e] for kk, vv in v.items()} for k, v in batch.items()}

@@ -81,3 +81,31 @@ class exact_cdist:
     def __exit__(self, *exc):
         self._torch.cdist, self._torch.argmin = self._cdist, self._argmin
         return False
+
+
+def load_reference_training():
+    """(LearnICPWeightPolicy class, eval_training_loss, eval_validation_loss) of the reference.
+
+    `mm_masking/icp_weight_policy.py:8` imports `neptune.types.File` (logging only, absent here): a
+    stub module stands in.  `train_icp_weights.py` pulls in the whole dataset / Neptune stack at
+    import time, so its two loss FUNCTIONS are compiled on their own from the unmodified source
+    file (AST extraction, nothing copied into the repo) with the reference's `radar_utils` names in
+    scope."""
+    import ast
+    _, _, _, ru = load_reference()
+    if "neptune" not in sys.modules:
+        nep = types.ModuleType("neptune"); nt = types.ModuleType("neptune.types")
+        nt.File = object; nep.types = nt
+        sys.modules["neptune"] = nep; sys.modules["neptune.types"] = nt
+    plt = sys.modules["matplotlib.pyplot"]
+    if not hasattr(plt, "figure"):
+        plt.figure = lambda *a, **k: None
+    import icp_weight_policy as ref_policy
+    import torch
+    path = os.path.join(REFERENCE_ROOT, "mm_masking", "train_icp_weights.py")
+    tree = ast.parse(open(path).read(), filename=path)
+    wanted = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in ("eval_training_loss", "eval_validation_loss")]
+    ns = {"torch": torch, "extract_bev_from_pts": ru.extract_bev_from_pts,
+          "radar_polar_to_cartesian_diff": ru.radar_polar_to_cartesian_diff}
+    exec(compile(ast.Module(body=wanted, type_ignores=[]), path, "exec"), ns)
+    return ref_policy.LearnICPWeightPolicy, ns["eval_training_loss"], ns["eval_validation_loss"]

@@ -65,3 +65,50 @@ def test_single_process_is_a_no_op():
     g = [torch.ones(2)]
     mdist.allreduce_mean_(g)
     assert g[0].tolist() == [1.0, 1.0]
+
+
+def _policy_worker(rank, ws, port, out):
+    """each rank runs the UNet on its half of the batch; the input normalisation must use the
+    min/max of the WHOLE batch (`icp_weight_policy.py:150-155`)"""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(ws))
+    dist.init_process_group("gloo", rank=rank, world_size=ws)
+    try:
+        from mm_masking_b200.icp_weight_policy import LearnICPWeightPolicy
+        torch.manual_seed(3)
+        model = LearnICPWeightPolicy({"device": "cpu", "range_input": False, "max_iter": 2}).eval()
+        g = torch.Generator().manual_seed(5)
+        fft = torch.rand((4, 32, 32), generator=g) * torch.tensor([1.0, 5.0, 0.2, 3.0]).view(4, 1, 1)
+        cfar = (torch.rand((4, 32, 32), generator=g) > 0.8).float()
+        s, e = mdist.shard_range(4, ws, rank)
+        scan = {"fft_data": fft[s:e].clone(), "fft_cfar": cfar[s:e].clone(), "raw_pc": torch.zeros(e - s, 2, 3),
+                "filtered_pc": torch.zeros(e - s, 2, 3)}
+        with torch.no_grad():
+            mask = model(scan, {"pc": torch.zeros(e - s, 2, 6)}, torch.eye(4).repeat(e - s, 1, 1), mask_only=True)
+        for norm in ("standardize",):
+            model.normalize_type = norm
+            with torch.no_grad():
+                m2 = model(scan, {"pc": torch.zeros(e - s, 2, 6)}, torch.eye(4).repeat(e - s, 1, 1), mask_only=True)
+        out[rank] = (mask.numpy(), m2.numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sharded_policy_forward_equals_full_batch():
+    ws = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_policy_worker, args=(ws, _free_port(), out), nprocs=ws, join=True)
+    from mm_masking_b200.icp_weight_policy import LearnICPWeightPolicy
+    torch.manual_seed(3)
+    model = LearnICPWeightPolicy({"device": "cpu", "range_input": False, "max_iter": 2}).eval()
+    g = torch.Generator().manual_seed(5)
+    fft = torch.rand((4, 32, 32), generator=g) * torch.tensor([1.0, 5.0, 0.2, 3.0]).view(4, 1, 1)
+    cfar = (torch.rand((4, 32, 32), generator=g) > 0.8).float()
+    scan = {"fft_data": fft, "fft_cfar": cfar, "raw_pc": torch.zeros(4, 2, 3), "filtered_pc": torch.zeros(4, 2, 3)}
+    args = (scan, {"pc": torch.zeros(4, 2, 6)}, torch.eye(4).repeat(4, 1, 1))
+    with torch.no_grad():
+        full = model(*args, mask_only=True).numpy()
+        model.normalize_type = "standardize"
+        full_std = model(*args, mask_only=True).numpy()
+    np.testing.assert_allclose(np.concatenate([out[0][0], out[1][0]]), full, atol=1e-6)
+    np.testing.assert_allclose(np.concatenate([out[0][1], out[1][1]]), full_std, atol=1e-5)
