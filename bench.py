@@ -171,7 +171,8 @@ def run_ours(args, wl, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=90))
 
     batch = make_batch(wl, seed=rank)
     N, n, m, K = wl["N"], wl["n"], wl["m"], wl["iters"]

@@ -50,7 +50,8 @@ def main():
     torch.backends.cudnn.benchmark = True            # UNet convolutions (PyTorch/cuDNN, not the product)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=90))
 
     s, e = mdist.shard_range(args.batch, world, rank)
     # every rank generates only its own pairs (seeded by the global pair index range)
@@ -106,7 +107,7 @@ def main():
 
     # ---- breakdown on rank 0 (one untimed extra step, events around the stages) -------------------
     breakdown = None
-    if rank == 0:
+    if world == 1:                      # the forward holds a collective: never run it on one rank only
         def ev():
             x = torch.cuda.Event(enable_timing=True); x.record(); return x
         bs, bm, bt = resident["loc_data"], resident["map_data"], resident["transforms"]

@@ -14,7 +14,10 @@
 //     host enqueues max_iterations rounds without synchronising.
 #include "mmb_common.cuh"
 
+#include <cooperative_groups.h>
 #include <vector>
+
+namespace cg = cooperative_groups;
 
 namespace mmb {
 
@@ -30,8 +33,10 @@ constexpr int NN_THREADS = 128;   // threads per NN block
 constexpr int NN_R = 4;           // queries per thread
 constexpr int NN_QB = NN_THREADS * NN_R;
 constexpr int NN_TILE = 512;      // targets per shared-memory tile
-constexpr int STEP_THREADS = 512;
-constexpr int BWD_THREADS = 512;
+constexpr int STEP_THREADS = 256;
+constexpr int STEP_MAX_CLUSTER = 8;  // CTAs per pair in the step kernel
+constexpr int BWD_THREADS = 256;
+constexpr int BWD_MAX_CLUSTER = 8;   // CTAs per pair in the adjoint sweep (portable cluster size)
 constexpr float PAD_COORD = __builtin_huge_valf();   // filter copy padding: never passes the filter
 
 constexpr int NN_SUB_STRIDE = 8;       // cold start: bound pass over every 8th target (DESIGN.md "cold start")
@@ -119,7 +124,8 @@ struct IcpWorkspace {
   int* conv;                     // (N)
   int* n_matched;                // (N) rows with w > thresh in the latest iteration
   int* n_start;                  // (N) rows with prior weight > thresh
-  int* counters;                 // [0] samples frozen, [1] done flag, [2] iterations executed
+  int* counters;                 // [0] pairs frozen, [1] 0 or (iteration in which the last pair froze) + 1, [2] iterations executed
+  int* allzero;                  // (N) this iteration's weights of the pair are all zero (ICP.py:215-218)
   // cell-grid backend
   double* geom;                  // (N,4) origin x, y, 1/cell, cell
   int* cell_start;               // (N, GRID_CELLS+2) first sorted slot of every Morton cell, of the outside bucket, m
@@ -149,6 +155,7 @@ static IcpWorkspace carve_workspace(void* base, const IcpPlan& pl) {
   w.n_matched = c.take<int>(pl.N);
   w.n_start = c.take<int>(pl.N);
   w.counters = c.take<int>(8);
+  w.allzero = c.take<int>(pl.N);
   const size_t Nm = pl.grid ? (size_t)pl.N * pl.m : 0, NG = pl.grid ? (size_t)pl.N : 0;
   w.geom = c.take<double>(NG * 4);
   w.cell_start = c.take<int>(NG * GRID_STRIDE);
@@ -364,6 +371,7 @@ struct NNArgs {
   const int* counters;       // done flag at [1], or nullptr
   double* pd2; int* pidx;    // (S,N,n)
   int N, n, m, mp, cols, tiles_per_slice, S;
+  int it;                    // iteration this search belongs to (for the done flag)
 };
 
 // BOUND = false: the search proper.  BOUND = true: the cold-start bound pass -- the same streaming
@@ -371,7 +379,7 @@ struct NNArgs {
 template <typename T, int DIM, bool BOUND>
 __global__ void __launch_bounds__(NN_THREADS) nn_search_kernel(NNArgs a) {
   const int qt = blockIdx.x, s = blockIdx.y, b = blockIdx.z;
-  if (a.counters && a.counters[1]) return;
+  if (a.counters && a.counters[1] && a.it >= a.counters[1]) return;   // all pairs froze in an EARLIER iteration
   if (a.frozen && a.frozen[b]) return;
 
   __shared__ __align__(128) float sx[2][NN_TILE];
@@ -685,7 +693,7 @@ struct GridNNArgs {
   const double* geom; const int* cell_start; const void* sorted;
   const int* idx_prev; const int* frozen; const int* counters;
   double* pd2; int* pidx;
-  int N, n, m, cols;
+  int N, n, m, cols, it;
 };
 
 // One WARP per query; the 32 lanes share the candidates of a cell range (coalesced 16-byte loads
@@ -727,7 +735,7 @@ __device__ __forceinline__ int clamp_cell(double v) {
 template <typename T, int DIM>
 __global__ void __launch_bounds__(GRIDNN_THREADS, MMB_GRID_MINBLOCKS) nn_grid_kernel(GridNNArgs a) {
   const int b = blockIdx.y;
-  if (a.counters && a.counters[1]) return;
+  if (a.counters && a.counters[1] && a.it >= a.counters[1]) return;   // all pairs froze in an EARLIER iteration
   if (a.frozen && a.frozen[b]) return;
   __shared__ double sP[12];
   __shared__ double sG[4];
@@ -963,11 +971,16 @@ __global__ void __launch_bounds__(STEP_THREADS) icp_step_kernel(StepArgs a) {
   constexpr int NV = NA + D + 4;     // A (upper), g, cost, sum w, matched, at-start
   constexpr int ROWS = ICP == MMB_PT2PT ? 3 : 1;
   __shared__ double scratch[NV * (STEP_THREADS / 32 + 1)];
+  __shared__ double part[NV], total[NV];
   __shared__ double sP[12];
-  __shared__ int s_flag;
+  // one thread-block cluster per pair: the CTAs split the points, rank 0 gathers the NV partial
+  // sums through distributed shared memory (rank order: deterministic) and does the solve
+  cg::cluster_group cluster = cg::this_cluster();
+  const int CL = (int)cluster.num_blocks(), crank = (int)cluster.block_rank();
 
-  const int b = blockIdx.x, tid = threadIdx.x, it = a.it;
-  if (a.w.counters[1]) return;                      // every pair converged earlier (ICP.py:249-250)
+  const int b = blockIdx.x / CL, tid = threadIdx.x, it = a.it;
+  const int gtid = crank * STEP_THREADS + tid, gstride = CL * STEP_THREADS;
+  if (a.w.counters[1] && it >= a.w.counters[1]) return;   // every pair converged in an earlier iteration (ICP.py:249-250)
   const int R = a.n * ROWS;
   T* wh = static_cast<T*>(a.weights_hist) + ((size_t)b * a.K + it) * R;
   T* dl = static_cast<T*>(a.deltas) + ((size_t)b * a.K + it) * 6;
@@ -976,9 +989,9 @@ __global__ void __launch_bounds__(STEP_THREADS) icp_step_kernel(StepArgs a) {
   if (a.w.frozen[b]) {
     // Prior weights are zero: w_sqrt = sqrt(1e-10) - 1e-5 == 0 exactly, so A = 1e-12 I, g = 0 and
     // the step is 0; the histories repeat the previous entries (ICP.py:215-224).
-    for (int i = tid; i < R; i += blockDim.x) wh[i] = it > 0 ? wh[i - (ptrdiff_t)R] : (T)0;
-    if (tid < 6) dl[tid] = (T)0;
-    if (tid == 0) {
+    for (int i = gtid; i < R; i += gstride) wh[i] = it > 0 ? wh[i - (ptrdiff_t)R] : (T)0;
+    if (crank == 0 && tid < 6) dl[tid] = (T)0;
+    if (crank == 0 && tid == 0) {
       *cs = from_double<T>(a.w.prev_cost[b]);
       a.w.n_matched[b] = 0;
       if (a.save) a.sv.active[(size_t)it * a.N + b] = 0;
@@ -998,7 +1011,7 @@ __global__ void __launch_bounds__(STEP_THREADS) icp_step_kernel(StepArgs a) {
 #pragma unroll
   for (int k = 0; k < NV; ++k) acc[k] = 0.0;
 
-  for (int i = tid; i < a.n; i += blockDim.x) {
+  for (int i = gtid; i < a.n; i += gstride) {
     const size_t o = (size_t)b * a.n + i;
     const int j = merge_partials(a.w.pd2, a.w.pidx, a.S, stride, o);
     a.w.idx_cur[o] = j;
@@ -1056,9 +1069,20 @@ __global__ void __launch_bounds__(STEP_THREADS) icp_step_kernel(StepArgs a) {
     }
   }
 
-  const double* tot = block_sum<NV>(acc, scratch);
+  {
+    const double* bt = block_sum<NV>(acc, scratch);
+    if (tid < NV) part[tid] = bt[tid];
+  }
+  cluster.sync();
+  if (crank == 0 && tid < NV) {
+    double s = 0.0;
+    for (int r = 0; r < CL; ++r) s += *cluster.map_shared_rank(&part[tid], r);
+    total[tid] = s;
+  }
+  __syncthreads();
+  const double* tot = total;
 
-  if (tid == 0) {
+  if (crank == 0 && tid == 0) {
     double A[D * D], g[D], x[D];
     int q = 0;
     for (int r0 = 0; r0 < D; ++r0)
@@ -1112,15 +1136,15 @@ __global__ void __launch_bounds__(STEP_THREADS) icp_step_kernel(StepArgs a) {
         if (a.w.match_ratio[b] == 0.0) a.w.match_ratio[b] = (double)matched / (double)(at_start > 0 ? at_start : 1);
         a.w.frozen[b] = 1;
         const int nf = atomicAdd(&a.w.counters[0], 1) + 1;
-        if (nf == a.N) a.w.counters[1] = 1;
+        if (nf == a.N) a.w.counters[1] = it + 1;                                    // later launches are no-ops
       }
     }
     a.w.counters[2] = it + 1;
-    s_flag = (tot[NA + D + 1] == 0.0 && it > 0) ? 1 : 0;
+    a.w.allzero[b] = (tot[NA + D + 1] == 0.0 && it > 0) ? 1 : 0;
   }
-  __syncthreads();
-  if (s_flag) {                        // all weights zero: repeat the previous row (ICP.py:215-218)
-    for (int i = tid; i < R; i += blockDim.x) wh[i] = wh[i - (ptrdiff_t)R];
+  cluster.sync();                      // rank 0 has read every partial and published the flag
+  if (__ldcg(a.w.allzero + b)) {       // all weights zero: repeat the previous row (ICP.py:215-218)
+    for (int i = gtid; i < R; i += gstride) wh[i] = wh[i - (ptrdiff_t)R];
   }
 }
 
@@ -1185,14 +1209,45 @@ struct BwdArgs {
 
 template <typename T> __device__ __forceinline__ void atomic_add_t(T* p, double v) { atomicAdd(p, from_double<T>(v)); }
 
+// Sum of 12 doubles per thread over every thread of the CLUSTER, left in tot[0..12) of every CTA.
+// Each CTA reduces its own threads (block_sum), publishes the 12 partials in its shared memory, and
+// after one cluster barrier every CTA adds the partials of all ranks in rank order through
+// distributed shared memory -- the same fixed order everywhere, so all CTAs hold identical bits and
+// the result does not depend on scheduling.  `part` is double-buffered by `parity`: a fast CTA may
+// already publish the next round while a slow one still reads this one.
+__device__ __forceinline__ const double* cluster_sum12(double (&acc)[12], double* scratch, double (*part)[12],
+                                                       double* tot, int& parity, cg::cluster_group& cluster) {
+  const double* t = block_sum<12>(acc, scratch);
+  if (threadIdx.x < 12) part[parity][threadIdx.x] = t[threadIdx.x];
+  cluster.sync();
+  if (threadIdx.x < 12) {
+    double s = 0.0;
+    const unsigned nb = cluster.num_blocks();
+    for (unsigned r = 0; r < nb; ++r) s += *cluster.map_shared_rank(&part[parity][threadIdx.x], r);
+    tot[threadIdx.x] = s;
+  }
+  __syncthreads();
+  parity ^= 1;
+  return tot;
+}
+
+// One thread-block CLUSTER per pair (up to 8 CTAs x 256 threads: one or two points per thread),
+// iterations in reverse inside the kernel; the 12-number pose adjoint of iteration k that iteration
+// k-1 needs is reduced across the cluster through distributed shared memory (cluster_sum12), and
+// every CTA repeats the tiny serial part (SO(3) adjoint + 3x3 / 6x6 solve) on identical inputs.
 template <typename T, int ICP, int DIM>
 __global__ void __launch_bounds__(BWD_THREADS) icp_backward_kernel(BwdArgs a) {
   constexpr int D = Dof<DIM>::D;
   __shared__ double scratch[12 * (BWD_THREADS / 32 + 1)];
+  __shared__ double part[2][12], tot12[12];
   __shared__ double sP[12], sCb[9], sRb[3], sLam[6], sDel[6];
   __shared__ int s_active;
+  cg::cluster_group cluster = cg::this_cluster();
+  const int CL = (int)cluster.num_blocks(), crank = (int)cluster.block_rank();
+  int parity = 0;
 
-  const int b = blockIdx.x, tid = threadIdx.x;
+  const int b = blockIdx.x / CL, tid = threadIdx.x;
+  const int i_first = crank * BWD_THREADS + tid, i_step = CL * BWD_THREADS;
   const T* src = static_cast<const T*>(a.source) + (size_t)b * a.n * 3;
   const T* tgt = static_cast<const T*>(a.target) + (size_t)b * a.m * a.cols;
   const T* wgt = a.has_weight ? static_cast<const T*>(a.weight) + (size_t)b * a.n : nullptr;
@@ -1211,7 +1266,7 @@ __global__ void __launch_bounds__(BWD_THREADS) icp_backward_kernel(BwdArgs a) {
     double acc[12];
 #pragma unroll
     for (int k = 0; k < 12; ++k) acc[k] = 0.0;
-    for (int i = tid; i < a.n; i += blockDim.x) {
+    for (int i = i_first; i < a.n; i += i_step) {
       double g0 = 0, g1 = 0, g2 = 0;
       if (gpc) { g0 = (double)gpc[i * 3]; g1 = (double)gpc[i * 3 + 1]; g2 = (double)gpc[i * 3 + 2]; }
       const double px = (double)src[i * 3], py = (double)src[i * 3 + 1], pz = DIM == 3 ? (double)src[i * 3 + 2] : 0.0;
@@ -1226,7 +1281,7 @@ __global__ void __launch_bounds__(BWD_THREADS) icp_backward_kernel(BwdArgs a) {
       }
       if (gw) gw[i] = (T)0;
     }
-    const double* tot = block_sum<12>(acc, scratch);
+    const double* tot = cluster_sum12(acc, scratch, part, tot12, parity, cluster);
     if (tid < 9) sCb[tid] = tot[tid] + (gT ? (double)gT[(tid / 3) * 4 + (tid % 3)] : 0.0);
     if (tid < 3) sRb[tid] = tot[9 + tid] + (gT ? (double)gT[tid * 4 + 3] : 0.0);
     __syncthreads();
@@ -1279,7 +1334,7 @@ __global__ void __launch_bounds__(BWD_THREADS) icp_backward_kernel(BwdArgs a) {
     double acc[12];
 #pragma unroll
     for (int q = 0; q < 12; ++q) acc[q] = 0.0;
-    for (int i = tid; i < a.n; i += blockDim.x) {
+    for (int i = i_first; i < a.n; i += i_step) {
       const int j = a.sv.idx_hist[(size_t)k * stride + (size_t)b * a.n + i];
       const double px = (double)src[i * 3], py = (double)src[i * 3 + 1], pz = DIM == 3 ? (double)src[i * 3 + 2] : 0.0;
       double ax, ay, az;
@@ -1375,13 +1430,14 @@ __global__ void __launch_bounds__(BWD_THREADS) icp_backward_kernel(BwdArgs a) {
         }
       }
     }
-    const double* tot = block_sum<12>(acc, scratch);
+    const double* tot = cluster_sum12(acc, scratch, part, tot12, parity, cluster);
     if (tid < 9) sCb[tid] += tot[tid];
     if (tid < 3) sRb[tid] += tot[9 + tid];
     __syncthreads();
   }
 
-  if (a.grad_T_init && tid < 16) {
+  cluster.sync();                       // no CTA may exit while another still reads its partials
+  if (a.grad_T_init && crank == 0 && tid < 16) {
     T* g = static_cast<T*>(a.grad_T_init) + (size_t)b * 16;
     const int i = tid / 4, j = tid % 4;
     double v = 0.0;
@@ -1462,7 +1518,7 @@ static int launch_grid_nn(const NNArgs& a, const IcpPlan& pl, const IcpWorkspace
   g.geom = w.geom; g.cell_start = w.cell_start; g.sorted = w.sorted;
   g.idx_prev = a.idx_prev; g.frozen = a.frozen; g.counters = a.counters;
   g.pd2 = a.pd2; g.pidx = a.pidx;
-  g.N = pl.N; g.n = pl.n; g.m = pl.m; g.cols = a.cols;
+  g.N = pl.N; g.n = pl.n; g.m = pl.m; g.cols = a.cols; g.it = a.it;
   dim3 grid((pl.n + GRIDNN_WARPS - 1) / GRIDNN_WARPS, pl.N);
   nn_grid_kernel<T, DIM><<<grid, GRIDNN_THREADS, 0, st>>>(g);
   return check_launch();
@@ -1553,11 +1609,22 @@ static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* s
 
   for (int it = 0; it < p->max_iterations; ++it) {
     na.idx_prev = it > 0 ? w.idx_cur : nullptr;
+    na.it = it;
     if (prof && it == 0 && !pl.sub_stride) prof->mark(2);
     if ((rc = pl.grid ? launch_grid_nn<T, DIM>(na, pl, w, st) : launch_nn<T, DIM>(na, pl, st))) return rc;
     if (prof) prof->mark(0);
     sa.it = it;
-    icp_step_kernel<T, ICP, DIM><<<pl.N, STEP_THREADS, 0, st>>>(sa);
+    {
+      int cl = 1;
+      while (cl < STEP_MAX_CLUSTER && cl * STEP_THREADS < pl.n) cl *= 2;
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3((unsigned)pl.N * cl); cfg.blockDim = dim3(STEP_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = cl; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr; cfg.numAttrs = 1;
+      cudaLaunchKernelEx(&cfg, icp_step_kernel<T, ICP, DIM>, sa);
+    }
     if ((rc = check_launch())) return rc;
     if (prof) prof->mark(1);
   }
@@ -1583,7 +1650,15 @@ static int run_backward(const mmb_icp_params* p, const IcpPlan& pl, const void* 
   a.rp.trim_dist = p->trim_dist; a.rp.loss_metric = p->loss_metric; a.rp.steep = p->tanh_steepness;
   a.N = pl.N; a.n = pl.n; a.m = pl.m; a.cols = p->target_cols; a.K = p->max_iterations;
   a.has_weight = p->has_weight && weight;
-  icp_backward_kernel<T, ICP, DIM><<<pl.N, BWD_THREADS, 0, st>>>(a);
+  int cl = 1;
+  while (cl < BWD_MAX_CLUSTER && cl * BWD_THREADS < pl.n) cl *= 2;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)pl.N * cl); cfg.blockDim = dim3(BWD_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = cl; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  if (cudaLaunchKernelEx(&cfg, icp_backward_kernel<T, ICP, DIM>, a) != cudaSuccess) return check_launch();
   return check_launch();
 }
 
@@ -1628,7 +1703,7 @@ static int run_nn_search(const IcpPlan& pl, int cols, int dim, const void* query
   na.bound_in = nullptr; na.bound_out = nullptr; na.bound_S = 0;
   na.pd2 = w.pd2; na.pidx = w.pidx;
   na.N = pl.N; na.n = pl.n; na.m = pl.m; na.mp = pl.mp; na.cols = cols;
-  na.tiles_per_slice = pl.tiles_per_slice; na.S = pl.S;
+  na.tiles_per_slice = pl.tiles_per_slice; na.S = pl.S; na.it = 0;
   if (pl.grid) {
     if ((rc = build_grid<T, DIM>(query, target, cols, pl, w, st))) return rc;
     if ((rc = launch_grid_nn<T, DIM>(na, pl, w, st))) return rc;
