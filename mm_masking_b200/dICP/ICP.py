@@ -185,7 +185,10 @@ class ICP:
         T, pc, deltas, weights, costs, converged, iterations, matched, iters_done = _IcpFunction.apply(
             source.to(dev), target.to(dev), T_init.to(dev), weight_arg, cfg)
 
-        it = int(iters_done.item())          # the one host sync of the call: history lengths (ICP.py:273-275)
+        if self.const_iter:
+            it = int(self.max_iterations)    # every pair runs all iterations (dICP_config.yaml:7): no host sync at all
+        else:
+            it = int(iters_done.item())      # the one host sync of the call: history lengths (ICP.py:273-275)
         if self.verbose:
             print("ICP converged in {} iterations".format(it))
         back = (lambda t: t) if out_device == dev else (lambda t: t.to(out_device))
