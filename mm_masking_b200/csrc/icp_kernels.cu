@@ -1205,6 +1205,7 @@ struct BwdArgs {
   void* grad_source; void* grad_target; void* grad_T_init; void* grad_weight;
   RowParams rp;
   int N, n, m, cols, K, has_weight;
+  int pre_iters;                 // iterations whose serial factors fit the dynamic shared memory
 };
 
 template <typename T> __device__ __forceinline__ void atomic_add_t(T* p, double v) { atomicAdd(p, from_double<T>(v)); }
@@ -1287,6 +1288,37 @@ __global__ void __launch_bounds__(BWD_THREADS) icp_backward_kernel(BwdArgs a) {
     __syncthreads();
   }
 
+  // Everything in the serial part of an iteration that does not depend on the running adjoint --
+  // exp(dphi^), the transposed left Jacobian of SO(3) and the inverse of the normal matrix -- is
+  // computed for ALL iterations up front, in parallel (one thread per (iteration, column)), so that
+  // the chain between iterations is a handful of 3x3 / DxD products.
+  extern __shared__ __align__(16) unsigned char bwd_dyn[];
+  constexpr int PRE = 18 + D * D;                  // doubles per iteration: dC[9], JlT[9], Ainv[D*D]
+  double* pre = reinterpret_cast<double*>(bwd_dyn);
+  const bool use_pre = a.pre_iters >= iters;
+  if (use_pre) {
+    for (int idx = tid; idx < iters * D; idx += blockDim.x) {
+      const int k = idx / D, c = idx % D;
+      const double* As = a.sv.A_hist + ((size_t)k * a.N + b) * 36;
+      double A[D * D], e[D], x[D];
+      for (int q = 0; q < D * D; ++q) A[q] = As[q];
+      for (int q = 0; q < D; ++q) e[q] = q == c ? 1.0 : 0.0;
+      solve_spd<D>(A, e, x);
+      for (int q = 0; q < D; ++q) pre[k * PRE + 18 + q * D + c] = x[q];       // column c of A^-1
+      if (c == 0) {
+        const double* dl = a.sv.delta_hist + ((size_t)k * a.N + b) * 6;
+        double phi[3] = {dl[0], dl[1], dl[2]}, col[3];
+        so3_exp(phi, pre + k * PRE);
+        for (int u = 0; u < 3; ++u) {
+          const double unit[3] = {u == 0 ? 1.0 : 0.0, u == 1 ? 1.0 : 0.0, u == 2 ? 1.0 : 0.0};
+          so3_left_jacobian_T_apply(phi, unit, col);
+          for (int q = 0; q < 3; ++q) pre[k * PRE + 9 + q * 3 + u] = col[q];     // column u of J_l^T
+        }
+      }
+    }
+    __syncthreads();
+  }
+
   for (int k = iters - 1; k >= 0; --k) {
     if (tid == 0) s_active = a.sv.active[(size_t)k * a.N + b];
     __syncthreads();
@@ -1296,34 +1328,63 @@ __global__ void __launch_bounds__(BWD_THREADS) icp_backward_kernel(BwdArgs a) {
     __syncthreads();
     if (tid == 0) {
       // C_{k+1} = dC^T C_k, r_{k+1} = r_k - dr, dC = exp(dphi^)
-      double dC[9], dCb[9], Cb_old[9], G[9], sv3[3], phib[3];
-      so3_exp(sDel, dC);
+      double dCl[9], dCb[9], Cb_old[9], G[9], sv3[3], phib[3];
+      const double* dC = dCl;
+      if (use_pre) dC = pre + k * PRE; else so3_exp(sDel, dCl);
+#pragma unroll
       for (int i = 0; i < 3; ++i)
+#pragma unroll
         for (int j = 0; j < 3; ++j) {
           double s1 = 0.0, s2 = 0.0;
+#pragma unroll
           for (int q = 0; q < 3; ++q) {
             s1 += sP[i * 3 + q] * sCb[j * 3 + q];        // dCbar = C_k Cbar_{k+1}^T
             s2 += dC[i * 3 + q] * sCb[q * 3 + j];        // Cbar_k (part) = dC Cbar_{k+1}
           }
           dCb[i * 3 + j] = s1; Cb_old[i * 3 + j] = s2;
         }
+#pragma unroll
       for (int i = 0; i < 3; ++i)
+#pragma unroll
         for (int j = 0; j < 3; ++j) {
           double s = 0.0;
+#pragma unroll
           for (int q = 0; q < 3; ++q) s += dCb[i * 3 + q] * dC[j * 3 + q];   // G = dCbar dC^T
           G[i * 3 + j] = s;
         }
       sv3[0] = G[7] - G[5]; sv3[1] = G[2] - G[6]; sv3[2] = G[3] - G[1];
-      so3_left_jacobian_T_apply(sDel, sv3, phib);
+      if (use_pre) {
+        const double* J = pre + k * PRE + 9;
+#pragma unroll
+        for (int q = 0; q < 3; ++q) phib[q] = J[q * 3] * sv3[0] + J[q * 3 + 1] * sv3[1] + J[q * 3 + 2] * sv3[2];
+      } else {
+        so3_left_jacobian_T_apply(sDel, sv3, phib);
+      }
       double d6b[6] = {phib[0], phib[1], phib[2], -sRb[0], -sRb[1], -sRb[2]};
-      double db[D], lam[D], A[D * D];
-      for (int q = 0; q < D; ++q) db[q] = d6b[dof_slot<DIM>(q)];
-      const double* As = a.sv.A_hist + ((size_t)k * a.N + b) * 36;
-      for (int q = 0; q < D * D; ++q) A[q] = As[q];
-      solve_spd<D>(A, db, lam);
+      double db[D], lam[D];
+#pragma unroll
+      for (int q = 0; q < D; ++q) db[q] = d6b[DIM == 2 ? q + 2 : q];
+      if (use_pre) {
+        const double* Ai = pre + k * PRE + 18;
+#pragma unroll
+        for (int q = 0; q < D; ++q) {
+          double sacc = 0.0;
+#pragma unroll
+          for (int c = 0; c < D; ++c) sacc += Ai[q * D + c] * db[c];
+          lam[q] = sacc;
+        }
+      } else {
+        double A[D * D];
+        const double* As = a.sv.A_hist + ((size_t)k * a.N + b) * 36;
+        for (int q = 0; q < D * D; ++q) A[q] = As[q];
+        solve_spd<D>(A, db, lam);
+      }
       // lambda = A^-1 deltabar on the solved slots
+#pragma unroll
       for (int q = 0; q < 6; ++q) sLam[q] = 0.0;
-      for (int q = 0; q < D; ++q) sLam[dof_slot<DIM>(q)] = lam[q];
+#pragma unroll
+      for (int q = 0; q < D; ++q) sLam[DIM == 2 ? q + 2 : q] = lam[q];
+#pragma unroll
       for (int q = 0; q < 9; ++q) sCb[q] = Cb_old[q];
     }
     __syncthreads();
@@ -1653,7 +1714,10 @@ static int run_backward(const mmb_icp_params* p, const IcpPlan& pl, const void* 
   int cl = 1;
   while (cl < BWD_MAX_CLUSTER && cl * BWD_THREADS < pl.n) cl *= 2;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)pl.N * cl); cfg.blockDim = dim3(BWD_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+  constexpr int PRE_BYTES = (18 + Dof<DIM>::D * Dof<DIM>::D) * (int)sizeof(double);
+  a.pre_iters = p->max_iterations <= 96 ? p->max_iterations : 0;      // <= 41 KB of dynamic shared memory
+  cfg.gridDim = dim3((unsigned)pl.N * cl); cfg.blockDim = dim3(BWD_THREADS); cfg.stream = st;
+  cfg.dynamicSmemBytes = (size_t)a.pre_iters * PRE_BYTES;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = cl; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
