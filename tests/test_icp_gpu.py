@@ -166,3 +166,27 @@ def test_cell_grid_backend_equals_brute_force(dtype, cfg):
                     src.grad, T0.grad, w.grad])
     for a, b in zip(*res):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("n,m", [(5000, 9000), (257, 300), (2049, 8192)])
+def test_cluster_kernels_with_several_points_per_thread(n, m):
+    """The step and backward kernels split the points of a pair over a thread-block cluster (8 x 256
+    threads): more than 2 048 points means several points per thread, fewer than 257 a single CTA.
+    Pose and weight gradient against the CPU oracle (fp64)."""
+    from mm_masking_b200 import synth
+    from mm_masking_b200.dICP import ICP
+    batch = synth.make_icp_batch(N=2, n=n, m=m, seed=29, pos=0.5, rot=0.1)
+    t64 = lambda a: torch.tensor(np.asarray(a, dtype=np.float64))
+    src, tgt, T0 = t64(batch["source"]).cuda(), t64(batch["target"]).cuda(), t64(batch["T_init"]).cuda()
+    w = t64(batch["weight"]).cuda().requires_grad_(True)
+    alg = ICP(icp_type="pt2pl", differentiable=True, max_iterations=3, tolerance=1e-9)
+    out = alg.icp(src, tgt, T0, weight=w, trim_dist=5.0, loss_fn={"name": "cauchy", "metric": 1.0}, dim=2)
+    out["T"].sum().backward()
+    w_ref = t64(batch["weight"]).requires_grad_(True)
+    ref = O.dicp(t64(batch["source"]), t64(batch["target"]), t64(batch["T_init"]), w_ref, icp_type="pt2pl",
+                 max_iterations=3, tolerance=1e-9, differentiable=True, trim_dist=5.0,
+                 loss_fn={"name": "cauchy", "metric": 1.0}, dim=2)
+    ref["T"].sum().backward()
+    assert (out["T"].detach().cpu() - ref["T"].detach()).abs().max() < 1e-10
+    scale = w_ref.grad.abs().max()
+    assert (w.grad.cpu() - w_ref.grad).abs().max() <= 1e-7 * scale
