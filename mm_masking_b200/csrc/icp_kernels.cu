@@ -721,11 +721,19 @@ constexpr int GRIDNN_WARPS = GRIDNN_THREADS / 32;
 #endif
 constexpr int GRID_SPLIT = 64;
 
-// an upper bound of sqrt(v), v >= 0, within 2^-22 relative (one MUFU instead of the fp64 routine)
-__device__ __forceinline__ double sqrt_upper(double v) {
-  return (double)__fsqrt_ru(__double2float_ru(v));
+// an upper bound of sqrt(v), v >= 0, within 2^-20 relative: one MUFU (sqrt.approx, max relative error
+// 2^-23) inflated by 2^-21, instead of the fp64 routine
+__device__ __forceinline__ float sqrt_upper_f(double v) {
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(__double2float_ru(v)));
+  return r * 1.00000048f;
 }
+__device__ __forceinline__ double sqrt_upper(double v) { return (double)sqrt_upper_f(v); }
 
+// the same for an fp32 coordinate (float -> int conversion saturates; NaN -> 0)
+__device__ __forceinline__ int clamp_cell_f(float v) {
+  return min(max(__float2int_rd(v), 0), GRID_G - 1);
+}
 __device__ __forceinline__ int clamp_cell(double v) {
   if (!(v >= 0.0)) return 0;
   if (v >= (double)GRID_G) return GRID_G - 1;
@@ -754,11 +762,15 @@ __global__ void __launch_bounds__(GRIDNN_THREADS, MMB_GRID_MINBLOCKS) nn_grid_ke
   double qx, qy, qz;
   transform_query<T, DIM>(src + (size_t)qi * 3, sP, qx, qy, qz);
   double fx = (qx - sG[0]) * sG[2], fy = (qy - sG[1]) * sG[2];
-  fx = fmin(fmax(fx, -1.0e12), 1.0e12); fy = fmin(fmax(fy, -1.0e12), 1.0e12);
+  if (!(fx > -1.0e12 && fx < 1.0e12)) fx = fx > 0.0 ? 1.0e12 : -1.0e12;      // also catches NaN
+  if (!(fy > -1.0e12 && fy < 1.0e12)) fy = fy > 0.0 ? 1.0e12 : -1.0e12;
   const bool inside = fx >= 0.0 && fx < (double)GRID_G && fy >= 0.0 && fy < (double)GRID_G;
-  const double gap = inside ? fmin(fmin(fx, (double)GRID_G - fx), fmin(fy, (double)GRID_G - fy)) : 0.0;   // cells
   constexpr double SLACK = 9.5367431640625e-07;            // 2^-20
   const double abs_slack = 1.0e-9 * (1.0 + fabs(fx) + fabs(fy));
+  // fp32 copies for the cell arithmetic (cell selection and sub-cell culling only decide WHICH targets
+  // are looked at; every fp32 quantity is widened by `ferr`, a bound on its rounding error in cells)
+  const float fxf = (float)fx, fyf = (float)fy;
+  const float ferr = 1.0e-6f * (300.0f + fabsf(fxf) + fabsf(fyf));
 
   double D2 = 1.0e308; int I = INT_MAX;                    // per-lane partial minimum
   // fp32 inputs: a conservative fp32 filter in front of the exact comparison.  With q~ = fl32(q)
@@ -804,7 +816,7 @@ __global__ void __launch_bounds__(GRIDNN_THREADS, MMB_GRID_MINBLOCKS) nn_grid_ke
   // GRID_SPLIT targets is split into its 4 x 4 sub-cells (16 consecutive Morton sub-ranges) and
   // only the sub-cells within dc2 (squared bound, cell units) of the query are scanned, runs of
   // adjacent sub-ranges in one go.
-  auto scan_cells = [&](int L, int x0, int x1, int y0, int y1, double dc2) {
+  auto scan_cells = [&](int L, int x0, int x1, int y0, int y1, float dc2) {
     const int nx = x1 - x0 + 1, nc = nx * (y1 - y0 + 1);
     const int iy = nx == 1 ? lane : (nx == 2 ? lane >> 1 : (lane * 11) >> 5), ix = lane - nx * iy;
     int s0 = 0, e0 = 0; unsigned k = 0;
@@ -828,9 +840,10 @@ __global__ void __launch_bounds__(GRIDNN_THREADS, MMB_GRID_MINBLOCKS) nn_grid_ke
       const int bnd_hi = __shfl_down_sync(0xffffffffu, bnd, 1);
       // Morton sub-index (lane) -> (u, v)
       const int u = (lane & 1) | ((lane >> 1) & 2), v = ((lane >> 1) & 1) | ((lane >> 2) & 2);
-      const double X = (double)(((x0 + icx) << L) + u * ss), Y = (double)(((y0 + icy) << L) + v * ss);
-      const double dx = fmax(fmax(X - fx, fx - (X + (double)ss)), 0.0), dy = fmax(fmax(Y - fy, fy - (Y + (double)ss)), 0.0);
-      unsigned keep = __ballot_sync(0xffffffffu, lane < 16 && bnd_hi > bnd && fma(dx, dx, dy * dy) <= dc2);
+      // lower bound of the distance to the sub-cell, fp32, each axis shortened by ferr (conservative)
+      const float X = (float)(((x0 + icx) << L) + u * ss), Y = (float)(((y0 + icy) << L) + v * ss), sf = (float)ss;
+      const float dx = fmaxf(fmaxf(X - fxf, fxf - (X + sf)) - ferr, 0.0f), dy = fmaxf(fmaxf(Y - fyf, fyf - (Y + sf)) - ferr, 0.0f);
+      unsigned keep = __ballot_sync(0xffffffffu, lane < 16 && bnd_hi > bnd && fmaf(dx, dx, dy * dy) <= dc2);
       while (keep) {
         const int t0 = __ffs(keep) - 1;
         const int len = __ffs(~(keep >> t0)) - 1;                        // run of adjacent sub-cells
@@ -876,10 +889,11 @@ __global__ void __launch_bounds__(GRIDNN_THREADS, MMB_GRID_MINBLOCKS) nn_grid_ke
     const int cx = clamp_cell(fx), cy = clamp_cell(fy);
     for (int L = 0; L <= GRID_BITS; ++L) {
       const int nb = GRID_G >> L, bx = cx >> L, by = cy >> L;
-      scan_cells(L, bx > 0 ? bx - 1 : 0, bx + 1 < nb ? bx + 1 : nb - 1, by > 0 ? by - 1 : 0, by + 1 < nb ? by + 1 : nb - 1, 1.0e300);
+      scan_cells(L, bx > 0 ? bx - 1 : 0, bx + 1 < nb ? bx + 1 : nb - 1, by > 0 ? by - 1 : 0, by + 1 < nb ? by + 1 : nb - 1, __int_as_float(0x7f800000));
       reduce();
       if (D2 < 1.0e300) {
         const double dc = sqrt_upper(D2) * sG[2] * (1.0 + SLACK) + abs_slack;   // cells, inflated
+        const double gap = fmin(fmin(fx, (double)GRID_G - fx), fmin(fy, (double)GRID_G - fy));   // to the grid border
         done = inside && dc < (double)(1 << L) && dc < gap;
         break;
       }
@@ -889,12 +903,14 @@ __global__ void __launch_bounds__(GRIDNN_THREADS, MMB_GRID_MINBLOCKS) nn_grid_ke
   }
   if (!done) {
     const double Dc = sqrt_upper(D2) * sG[2] * (1.0 + SLACK) + abs_slack;  // cells, inflated
-    const int xlo = clamp_cell(fx - Dc), xhi = clamp_cell(fx + Dc), ylo = clamp_cell(fy - Dc), yhi = clamp_cell(fy + Dc);
-    int L = 0;
+    const float Dcf = __double2float_ru(Dc) + ferr;                  // cells, fp32, widened
+    const int xlo = clamp_cell_f(fxf - Dcf), xhi = clamp_cell_f(fxf + Dcf), ylo = clamp_cell_f(fyf - Dcf), yhi = clamp_cell_f(fyf + Dcf);
+    const int span = max(xhi - xlo, yhi - ylo);
+    int L = span <= 2 ? 0 : 30 - __clz(span);                          // span >> L is 2 or 3: at most two more steps
     while (((xhi >> L) - (xlo >> L)) > 2 || ((yhi >> L) - (ylo >> L)) > 2) ++L;
     // cells entirely left/right/above/below the square hold nothing (clamping only ADDS cells)
     if (fx + Dc >= 0.0 && fx - Dc < (double)GRID_G && fy + Dc >= 0.0 && fy - Dc < (double)GRID_G)
-      scan_cells(L, xlo >> L, xhi >> L, ylo >> L, yhi >> L, Dc * Dc);
+      scan_cells(L, xlo >> L, xhi >> L, ylo >> L, yhi >> L, __fmul_ru(Dcf, Dcf) * 1.000001f);
     if (!(fx - Dc >= 0.0 && fx + Dc < (double)GRID_G && fy - Dc >= 0.0 && fy + Dc < (double)GRID_G)) scan_outside();
     reduce();
   }
