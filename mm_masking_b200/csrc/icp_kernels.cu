@@ -19,6 +19,13 @@
 
 namespace cg = cooperative_groups;
 
+// Programmatic dependent launch (sm_90+): a kernel launched with the programmatic-stream-serialization
+// attribute may become resident while its predecessor in the stream drains; it must not touch the
+// predecessor's output before pdl_wait().  pdl_wait() is a no-op for a normal launch.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// lets the next kernel of the stream (if it allows it) be scheduled into the slots this grid leaves free
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 namespace mmb {
 
 static thread_local char g_last_cuda_error[256] = "";
@@ -372,6 +379,7 @@ struct NNArgs {
   double* pd2; int* pidx;    // (S,N,n)
   int N, n, m, mp, cols, tiles_per_slice, S;
   int it;                    // iteration this search belongs to (for the done flag)
+  int pdl;                   // launched right after a kernel of this library (programmatic dependent launch allowed)
 };
 
 // BOUND = false: the search proper.  BOUND = true: the cold-start bound pass -- the same streaming
@@ -742,6 +750,8 @@ __device__ __forceinline__ int clamp_cell(double v) {
 
 template <typename T, int DIM>
 __global__ void __launch_bounds__(GRIDNN_THREADS, MMB_GRID_MINBLOCKS) nn_grid_kernel(GridNNArgs a) {
+  pdl_wait();
+  pdl_trigger();
   const int b = blockIdx.y;
   if (a.counters && a.counters[1] && a.it >= a.counters[1]) return;   // all pairs froze in an EARLIER iteration
   if (a.frozen && a.frozen[b]) return;
@@ -991,6 +1001,8 @@ __global__ void __launch_bounds__(STEP_THREADS) icp_step_kernel(StepArgs a) {
   __shared__ double sP[12];
   // one thread-block cluster per pair: the CTAs split the points, rank 0 gathers the NV partial
   // sums through distributed shared memory (rank order: deterministic) and does the solve
+  pdl_wait();
+  pdl_trigger();
   cg::cluster_group cluster = cg::this_cluster();
   const int CL = (int)cluster.num_blocks(), crank = (int)cluster.block_rank();
 
@@ -1597,7 +1609,13 @@ static int launch_grid_nn(const NNArgs& a, const IcpPlan& pl, const IcpWorkspace
   g.pd2 = a.pd2; g.pidx = a.pidx;
   g.N = pl.N; g.n = pl.n; g.m = pl.m; g.cols = a.cols; g.it = a.it;
   dim3 grid((pl.n + GRIDNN_WARPS - 1) / GRIDNN_WARPS, pl.N);
-  nn_grid_kernel<T, DIM><<<grid, GRIDNN_THREADS, 0, st>>>(g);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = dim3(GRIDNN_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = a.pdl ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, nn_grid_kernel<T, DIM>, g);
   return check_launch();
 }
 
@@ -1686,7 +1704,7 @@ static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* s
 
   for (int it = 0; it < p->max_iterations; ++it) {
     na.idx_prev = it > 0 ? w.idx_cur : nullptr;
-    na.it = it;
+    na.it = it; na.pdl = it > 0 ? 1 : 0;
     if (prof && it == 0 && !pl.sub_stride) prof->mark(2);
     if ((rc = pl.grid ? launch_grid_nn<T, DIM>(na, pl, w, st) : launch_nn<T, DIM>(na, pl, st))) return rc;
     if (prof) prof->mark(0);
@@ -1696,10 +1714,12 @@ static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* s
       while (cl < STEP_MAX_CLUSTER && cl * STEP_THREADS < pl.n) cl *= 2;
       cudaLaunchConfig_t cfg = {};
       cfg.gridDim = dim3((unsigned)pl.N * cl); cfg.blockDim = dim3(STEP_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = st;
-      cudaLaunchAttribute attr[1];
+      cudaLaunchAttribute attr[2];
       attr[0].id = cudaLaunchAttributeClusterDimension;
       attr[0].val.clusterDim.x = cl; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-      cfg.attrs = attr; cfg.numAttrs = 1;
+      attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[1].val.programmaticStreamSerializationAllowed = pl.grid ? 1 : 0;   // the grid search before it calls pdl_wait()
+      cfg.attrs = attr; cfg.numAttrs = 2;
       cudaLaunchKernelEx(&cfg, icp_step_kernel<T, ICP, DIM>, sa);
     }
     if ((rc = check_launch())) return rc;
@@ -1783,7 +1803,7 @@ static int run_nn_search(const IcpPlan& pl, int cols, int dim, const void* query
   na.bound_in = nullptr; na.bound_out = nullptr; na.bound_S = 0;
   na.pd2 = w.pd2; na.pidx = w.pidx;
   na.N = pl.N; na.n = pl.n; na.m = pl.m; na.mp = pl.mp; na.cols = cols;
-  na.tiles_per_slice = pl.tiles_per_slice; na.S = pl.S; na.it = 0;
+  na.tiles_per_slice = pl.tiles_per_slice; na.S = pl.S; na.it = 0; na.pdl = 0;
   if (pl.grid) {
     if ((rc = build_grid<T, DIM>(query, target, cols, pl, w, st))) return rc;
     if ((rc = launch_grid_nn<T, DIM>(na, pl, w, st))) return rc;
