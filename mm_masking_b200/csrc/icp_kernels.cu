@@ -757,17 +757,26 @@ __global__ void __launch_bounds__(GRIDNN_THREADS, MMB_GRID_MINBLOCKS) nn_grid_ke
   if (a.frozen && a.frozen[b]) return;
   __shared__ double sP[12];
   __shared__ double sG[4];
+  struct Bases { const T* src; const T* tgt; const int* start; const void* sorted; };
+  __shared__ Bases sB;
   const int tid = threadIdx.x, lane = tid & 31;
   if (tid < 12) sP[tid] = a.pose[(size_t)b * 12 + tid];
   if (tid < 4) sG[tid] = a.geom[(size_t)b * 4 + tid];
+  if (tid == 32) {
+    sB.src = static_cast<const T*>(a.source) + (size_t)b * a.n * 3;
+    sB.tgt = static_cast<const T*>(a.target) + (size_t)b * a.m * a.cols;
+    sB.start = a.cell_start + (size_t)b * GRID_STRIDE;
+    sB.sorted = static_cast<const SortedPoint<T>*>(a.sorted) + (size_t)b * a.m;
+  }
   __syncthreads();
   const int qi = blockIdx.x * GRIDNN_WARPS + (tid >> 5);
   if (qi >= a.n) return;                                   // whole warp
 
-  const T* src = static_cast<const T*>(a.source) + (size_t)b * a.n * 3;
-  const T* tgt = static_cast<const T*>(a.target) + (size_t)b * a.m * a.cols;
-  const int* start = a.cell_start + (size_t)b * GRID_STRIDE;
-  const SortedPoint<T>* sorted = static_cast<const SortedPoint<T>*>(a.sorted) + (size_t)b * a.m;
+  // per-pair base pointers: computed once per block and parked in shared memory -- at 32 registers per
+  // thread the compiler otherwise re-derives them (64-bit multiply-adds) inside the candidate loop
+  const T* src = sB.src; const T* tgt = sB.tgt;
+  const int* start = sB.start;
+  const SortedPoint<T>* sorted = static_cast<const SortedPoint<T>*>(sB.sorted);
 
   double qx, qy, qz;
   transform_query<T, DIM>(src + (size_t)qi * 3, sP, qx, qy, qz);
@@ -798,9 +807,10 @@ __global__ void __launch_bounds__(GRIDNN_THREADS, MMB_GRID_MINBLOCKS) nn_grid_ke
     thr = __double2float_ru(t);
   };
   auto scan = [&](int s0, int e0) {
-    for (int p = s0 + lane; p < e0; p += 32) {
+    const SortedPoint<T>* ptr = sorted + (s0 + lane);                 // walks the range: one 64-bit add per round
+    for (int left = e0 - s0 - lane; left > 0; left -= 32, ptr += 32) {
       if (FILTER) {
-        const float4 v = __ldg(reinterpret_cast<const float4*>(sorted + p));
+        const float4 v = __ldg(reinterpret_cast<const float4*>(ptr));
         const float dxf = v.x - qxf, dyf = v.y - qyf;
         float f = fmaf(dyf, dyf, dxf * dxf);
         if (DIM == 3) { const float dzf = v.z - qzf; f = fmaf(dzf, dzf, f); }
@@ -813,7 +823,7 @@ __global__ void __launch_bounds__(GRIDNN_THREADS, MMB_GRID_MINBLOCKS) nn_grid_ke
         }
       } else {
         double tx, ty, tz; int j;
-        load_sorted(sorted + p, tx, ty, tz, j);
+        load_sorted(ptr, tx, ty, tz, j);
         const double dx = tx - qx, dy = ty - qy;
         double e2 = fma(dy, dy, __dmul_rn(dx, dx));
         if (DIM == 3) { const double dz = tz - qz; e2 = fma(dz, dz, e2); }
