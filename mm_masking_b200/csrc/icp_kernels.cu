@@ -727,7 +727,10 @@ constexpr int GRIDNN_WARPS = GRIDNN_THREADS / 32;
 #ifndef MMB_GRID_MINBLOCKS
 #define MMB_GRID_MINBLOCKS 8
 #endif
-constexpr int GRID_SPLIT = 64;
+#ifndef MMB_GRID_SPLIT
+#define MMB_GRID_SPLIT 128
+#endif
+constexpr int GRID_SPLIT = MMB_GRID_SPLIT;
 
 // an upper bound of sqrt(v), v >= 0, within 2^-20 relative: one MUFU (sqrt.approx, max relative error
 // 2^-23) inflated by 2^-21, instead of the fp64 routine
