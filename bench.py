@@ -12,7 +12,9 @@ configs[2]): 32 pairs per GPU, 2 000 radar points vs 50 000 lidar map points, 10
 
   value  pairs/s with inputs resident in HBM (CUDA events per step, L2 flushed between steps)
   e2e    pairs/s through the same public call with HOST (pinned) inputs: H2D of source, target,
-         T_init, weight and D2H of T and d(loss)/d(weight) inside the timed region
+         T_init, weight and D2H of T and d(loss)/d(weight) inside the timed region, every step;
+         fed through mm_masking_b200.prefetch.DevicePrefetcher (the upload of step k+1 runs on a
+         copy stream under the kernels of step k); one event pair around all K steps
   roofline       the dominant kernel of the default path, the exact cell-grid search
                  (nn_grid_kernel): algorithmic bytes per launch / its CUDA-event duration against
                  the measured HBM peak, flagged work-avoiding
@@ -164,6 +166,7 @@ def run_ours(args, wl, rank, world, local_rank):
     import torch.distributed as dist
     from mm_masking_b200 import _capi, dist as mdist
     from mm_masking_b200.dICP import ICP
+    from mm_masking_b200.prefetch import DevicePrefetcher
     from mm_masking_b200.dICP.ICP import _IcpFunction  # noqa: F401  (same code path as ICP.icp)
 
     _capi.require_cuda()
@@ -195,12 +198,9 @@ def run_ours(args, wl, rank, world, local_rank):
         out["T"].sum().backward()
         return out
 
-    def step_e2e():
-        src = host["source"].to(dev, non_blocking=True)
-        tgt = host["target"].to(dev, non_blocking=True)
-        T0 = host["T_init"].to(dev, non_blocking=True)
-        w = host["weight"].to(dev, non_blocking=True).requires_grad_(True)
-        out = alg.icp(src, tgt, T0, weight=w, **call)
+    def step_e2e(b):
+        w = b["weight"].requires_grad_(True)
+        out = alg.icp(b["source"], b["target"], b["T_init"], weight=w, **call)
         out["T"].sum().backward()
         out_T.copy_(out["T"].detach(), non_blocking=True)
         out_gw.copy_(w.grad, non_blocking=True)
@@ -231,7 +231,35 @@ def run_ours(args, wl, rank, world, local_rank):
         sampler.start()
         time.sleep(0.3)
     ms_res, t0, t1 = timed(step_resident, args.steps, args.warmup)
-    ms_e2e, _, t1 = timed(step_e2e, args.steps, max(1, args.warmup // 2))
+    # e2e: the same call fed from pinned HOST tensors through the package's DevicePrefetcher (what
+    # a user's loop does): every step uploads its own source/target/T_init/weight (no reuse across
+    # steps; the upload of step k+1 runs on a copy stream under the kernels of step k) and reads T
+    # and d/d weight back.  ONE event pair around all K steps, L2 flushes included, so nothing that
+    # happens between steps escapes the clock.
+    e2e_warm = max(2, args.warmup // 2)
+    pre = DevicePrefetcher((host for _ in range(e2e_warm + args.steps + 1)), dev)
+    for _ in range(e2e_warm):
+        step_e2e(next(pre))
+    barrier()
+    up0 = pre.bytes_uploaded
+    ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ea.record()
+    for _ in range(args.steps):
+        flush.fill_(1)
+        step_e2e(next(pre))
+    eb.record()
+    barrier()
+    t1 = time.time()
+    h2d_per_step = (pre.bytes_uploaded - up0) // args.steps
+    ms_e2e = mdist.max_over_ranks(ea.elapsed_time(eb), device=dev) / args.steps
+    # for comparison: the reference's loop shape, upload on the compute stream in front of each call
+    ea.record()
+    for _ in range(args.steps):
+        flush.fill_(1)
+        step_e2e({k: v.to(dev, non_blocking=True) for k, v in host.items()})
+    eb.record()
+    barrier()
+    ms_e2e_serial = mdist.max_over_ranks(ea.elapsed_time(eb), device=dev) / args.steps
     clocks = None
     if sampler:
         sampler.stop()
@@ -358,7 +386,10 @@ def run_ours(args, wl, rank, world, local_rank):
                    "l2": "flushed between steps (256 MiB fill, untimed); per-step CUDA events",
                    "parallelism": f"independent pairs, {world} rank(s), no data-path collective"},
         "e2e": {"value": world * N / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+                "h2d_bytes_per_step": h2d_per_step, "d2h_bytes_per_step": d2h,
+                "serial_upload_value": world * N / (ms_e2e_serial * 1e-3),
+                "overlap": "H2D of step k+1 on a copy stream under the kernels of step k (DevicePrefetcher); "
+                           "K uploads inside the timed region, L2 flush time included"},
         "gpu_launches": launches_per_step * args.steps * 2,
         "roofline": roofline,
         "roofline_exhaustive_nn": roofline_brute,
