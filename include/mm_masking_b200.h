@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define MMB_ABI_VERSION 2
+#define MMB_ABI_VERSION 3
 
 typedef enum mmb_status {
   MMB_OK = 0,
@@ -211,7 +211,9 @@ int mmb_cfar_mask(const mmb_cfar_params* p, const void* scan, void* mask, void* 
 
 /* Peak extraction.  Replaces radar_utils.py:71-106 (`extract_pc`, with
  * `mean_peaks_parallel_fast` :167-185 and `pol_2_cart` :187-195).  Two phases because the
- * number of points is data dependent: count -> (caller reads totals, allocates) -> write.
+ * number of points is data dependent: count -> (caller reads totals, allocates) -> write.  The
+ * count call evaluates every azimuth row once and parks its peak entries in the workspace; the
+ * write call only assembles the points from them, so the workspace must not be touched in between.
  * fused != 0: the first buffer is the SCAN and the CFAR mask of `cfar` is evaluated on the fly. */
 typedef struct mmb_extract_params {
   int32_t B, A, R;
@@ -221,14 +223,15 @@ typedef struct mmb_extract_params {
   double res, steep_fact;
   mmb_cfar_params cfar;    /* used when fused */
 } mmb_extract_params;
-size_t mmb_extract_workspace_bytes(int32_t B, int32_t A);
+size_t mmb_extract_workspace_bytes(const mmb_extract_params* p);
 /*   totals (B) int32 device: number of non-zero peak entries per scan (= 2 x points) */
 int mmb_extract_count(const mmb_extract_params* p, const void* mask_or_scan, void* workspace,
                       size_t workspace_bytes, int32_t* totals, void* stream);
-/*   same workspace as the count call.  ent_val (B,entry_cap) dtype, ent_row (B,entry_cap) int32:
- *   scratch for the peak entries; azimuths (B,A); T_ab (B,4,4) or NULL;
+/*   same workspace as the count call, contents intact.  ent_val (B,entry_cap) dtype, ent_row
+ *   (B,entry_cap) int32: the peak entries (value, azimuth row) in flattened order, for inspection;
+ *   azimuths (B,A); T_ab (B,4,4) or NULL;
  *   points_out (B,out_cap,3): scan b holds totals[b]/2 points, azimuth-major, range ascending. */
-int mmb_extract_write(const mmb_extract_params* p, const void* mask_or_scan, const void* azimuths,
+int mmb_extract_write(const mmb_extract_params* p, const void* azimuths,
                       const void* T_ab, void* workspace, size_t workspace_bytes,
                       int32_t entry_cap, void* ent_val, int32_t* ent_row, int32_t out_cap,
                       void* points_out, void* stream);

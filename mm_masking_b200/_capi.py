@@ -76,9 +76,9 @@ SIGNATURES = {
     "mmb_bev_from_points": (C.c_int, [C.c_int32] * 5 + [C.c_double, C.c_double, _P, _P, _P]),
     "mmb_cfar_columns": (C.c_int, [C.POINTER(CfarParams)] + [C.POINTER(C.c_int32)] * 3),
     "mmb_cfar_mask": (C.c_int, [C.POINTER(CfarParams), _P, _P, _P]),
-    "mmb_extract_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "mmb_extract_workspace_bytes": (C.c_size_t, [C.POINTER(ExtractParams)]),
     "mmb_extract_count": (C.c_int, [C.POINTER(ExtractParams), _P, _P, C.c_size_t, _P, _P]),
-    "mmb_extract_write": (C.c_int, [C.POINTER(ExtractParams), _P, _P, _P, _P, C.c_size_t, C.c_int32, _P, _P,
+    "mmb_extract_write": (C.c_int, [C.POINTER(ExtractParams), _P, _P, _P, C.c_size_t, C.c_int32, _P, _P,
                                     C.c_int32, _P, _P]),
     "mmb_kstrong_workspace_bytes": (C.c_size_t, [C.POINTER(KStrongParams)]),
     "mmb_kstrong_select": (C.c_int, [C.POINTER(KStrongParams), _P, _P, C.c_size_t, _P, _P]),
@@ -107,7 +107,7 @@ def load_library(path: str | None = None):
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)
         fn.restype, fn.argtypes = res, args
-    if lib.mmb_abi_version() != 2:
+    if lib.mmb_abi_version() != 3:
         raise MmbError("libmm_masking_b200.so ABI version mismatch")
     _lib = lib
     return lib

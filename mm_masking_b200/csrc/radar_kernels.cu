@@ -322,10 +322,13 @@ __global__ void __launch_bounds__(ROW_THREADS) cfar_mask_kernel(CfarArgs a) {
 //     v[k] = arr[k] * z[k+1] + arr[k+1] * z[k]   (k < R-1),  v[R-1] = 0,
 // z = (arr == 0) (non-diff) or 1 - tanh(steep * arr) (diff).  The non-zero v of the flattened
 // scan, in order, are paired (2i, 2i+1) and averaged into (rho, phi) -> (rho cos phi, rho sin phi, 0).
-// Three passes, all one block per azimuth row with arr staged in shared memory:
-//   count:  non-zero v per row                       -> counts (B*A)
+// Three kernels:
+//   rows:    one block per azimuth row, arr staged in shared memory: the non-zero v of the row, in range
+//            order, go to the row's slot of a staging area (rowcap values per row; only the entries
+//            that exist are written) and their number to counts (B*A).  The row is evaluated ONCE.
 //   offsets: exclusive scan of the A counts per scan -> offsets (B, A+1)      [one block per scan]
-//   write:  (value, row) of every non-zero v at its flattened ordinal; then one thread per point.
+//   points:  one thread per point: entries (2i, 2i+1) of the flattened scan are located through the
+//            offsets (binary search over the rows) and read from the staging area.
 // The row source is either a mask tensor (the reference's extract_pc signature) or the CFAR mask
 // evaluated on the fly from the scan (fused cfar + extraction: the mask is never written).
 struct PeakArgs {
@@ -336,10 +339,16 @@ struct PeakArgs {
   float res;
   int diff; double steep;
   int* counts;                  // (rows)
-  const int* offsets;           // (B, A+1)
-  void* ent_val; int* ent_row;  // (B, cap) entries
-  int cap;
+  void* stage; int rowcap;      // (rows, rowcap) working dtype: the row's non-zero v in range order
 };
+
+// columns [c0, c1) that can hold a non-zero v: with the fused source the mask is zero outside
+// [mincol, maxcol), so entries can only sit in [mincol-1, maxcol)
+__host__ __device__ __forceinline__ void peak_span(const PeakArgs& a, bool fused, int& c0, int& c1) {
+  c0 = fused ? (a.cfar.mincol - 1 > 0 ? a.cfar.mincol - 1 : 0) : 0;
+  c1 = fused ? (a.cfar.maxcol < a.R ? a.cfar.maxcol : a.R) : a.R;
+  if (c1 < c0) c1 = c0;
+}
 
 template <typename T, bool FUSED>
 __device__ __forceinline__ void stage_arr(const PeakArgs& a, size_t row, T* arr, double* pre, double* wt) {
@@ -376,7 +385,7 @@ __device__ __forceinline__ T peak_value(const PeakArgs& a, const T* arr, int k) 
   return add_rn(mul_rn(x0, z1), mul_rn(x1, z0));
 }
 
-template <typename T, bool FUSED, bool WRITE>
+template <typename T, bool FUSED>
 __global__ void __launch_bounds__(ROW_THREADS) peak_rows_kernel(PeakArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* pre = reinterpret_cast<double*>(smem_raw);                       // fused source only
@@ -386,29 +395,21 @@ __global__ void __launch_bounds__(ROW_THREADS) peak_rows_kernel(PeakArgs a) {
   const size_t row = blockIdx.x;
   stage_arr<T, FUSED>(a, row, arr, pre, wt);
 
-  // each thread owns a contiguous chunk so that ordinals follow the range order; with the fused
-  // source the mask is zero outside [mincol, maxcol), so entries can only sit in [mincol-1, maxcol)
-  const int c0 = FUSED ? max(a.cfar.mincol - 1, 0) : 0, c1 = FUSED ? min(a.cfar.maxcol, a.R) : a.R;
+  // each thread owns a contiguous chunk so that ordinals follow the range order
+  int c0, c1;
+  peak_span(a, FUSED, c0, c1);
   const int chunk = (c1 - c0 + blockDim.x - 1) / blockDim.x;
   const int s = c0 + threadIdx.x * chunk, e = min(s + chunk, c1);
   int cnt = 0;
   for (int k = s; k < e; ++k) cnt += peak_value<T>(a, arr, k) != (T)0 ? 1 : 0;
   int total;
   int pos = block_exclusive_scan<int>(cnt, wi, total);
-  if (!WRITE) {
-    if (threadIdx.x == 0) a.counts[row] = total;
-    return;
-  }
-  const int b = (int)(row / a.A), r = (int)(row % a.A);
-  pos += a.offsets[(size_t)b * (a.A + 1) + r];
-  T* ev = static_cast<T*>(a.ent_val) + (size_t)b * a.cap;
-  int* er = a.ent_row + (size_t)b * a.cap;
+  if (threadIdx.x == 0) a.counts[row] = total;
+  if (cnt == 0) return;
+  T* sv = static_cast<T*>(a.stage) + row * (size_t)a.rowcap;               // total <= c1 - c0 = rowcap
   for (int k = s; k < e; ++k) {
     const T v = peak_value<T>(a, arr, k);
-    if (v != (T)0) {
-      if (pos < a.cap) { ev[pos] = v; er[pos] = r; }
-      ++pos;
-    }
+    if (v != (T)0) sv[pos++] = v;
   }
 }
 
@@ -433,18 +434,32 @@ __global__ void row_offsets_kernel(const int* __restrict__ counts, int A, int* _
 }
 
 // One thread per point: entries (2i, 2i+1) -> (rho, phi) -> xyz (radar_utils.py:96-104, 187-195).
+// The two entries are consecutive in the FLATTENED scan, so the second may sit in a later row.
 template <typename T>
-__global__ void peak_points_kernel(const T* __restrict__ ent_val, const int* __restrict__ ent_row,
-                                   const int* __restrict__ offsets, const T* __restrict__ azimuths,
-                                   const T* __restrict__ T_ab, int A, int cap, int out_cap, T* __restrict__ out) {
+__global__ void peak_points_kernel(const T* __restrict__ stage, int rowcap, const int* __restrict__ offsets,
+                                   const T* __restrict__ azimuths, const T* __restrict__ T_ab, int A, int cap,
+                                   int out_cap, T* __restrict__ ent_val, int* __restrict__ ent_row,
+                                   T* __restrict__ out) {
   const int b = blockIdx.y;
-  const int npts = offsets[(size_t)b * (A + 1) + A] / 2;
+  const int* off = offsets + (size_t)b * (A + 1);
+  const int npts = off[A] / 2;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= npts || i >= out_cap || 2 * i + 1 >= cap) return;
-  const T* ev = ent_val + (size_t)b * cap;
-  const int* er = ent_row + (size_t)b * cap;
-  const T rho = div_rn(add_rn(ev[2 * i + 1], ev[2 * i]), (T)2);
-  const T phi = div_rn(add_rn(azimuths[(size_t)b * A + er[2 * i + 1]], azimuths[(size_t)b * A + er[2 * i]]), (T)2);
+  const int e0 = 2 * i, e1 = e0 + 1;
+  int r0 = 0, hi = A;                            // off[r0] <= e0 < off[hi]; empty rows share an offset,
+  while (hi - r0 > 1) {                          // so the LAST row with off <= e0 is the one holding e0
+    const int mid = (r0 + hi) >> 1;
+    if (off[mid] <= e0) r0 = mid; else hi = mid;
+  }
+  int r1 = r0;
+  while (off[r1 + 1] <= e1) ++r1;                // e1 < off[A]: terminates
+  const T* sb = stage + (size_t)b * A * rowcap;
+  const T v0 = sb[(size_t)r0 * rowcap + (e0 - off[r0])], v1 = sb[(size_t)r1 * rowcap + (e1 - off[r1])];
+  T* ev = ent_val + (size_t)b * cap;
+  int* er = ent_row + (size_t)b * cap;
+  ev[e0] = v0; ev[e1] = v1; er[e0] = r0; er[e1] = r1;
+  const T rho = div_rn(add_rn(v1, v0), (T)2);
+  const T phi = div_rn(add_rn(azimuths[(size_t)b * A + r1], azimuths[(size_t)b * A + r0]), (T)2);
   // cos/sin: correctly rounded (evaluated in fp64, rounded once), then the reference's product;
   // the host libraries the reference runs on differ from each other by an ulp here.
   T x = mul_rn(rho, (T)cos((double)phi)), y = mul_rn(rho, (T)sin((double)phi)), z = (T)0;
@@ -608,40 +623,46 @@ template <typename K> static int opt_in_smem(K kernel, size_t bytes) {
   return MMB_OK;
 }
 
-struct ExtractWs { int* counts; int* offsets; size_t bytes; };
-static ExtractWs carve_extract(void* base, int B, int A) {
+struct ExtractWs { int* counts; int* offsets; void* stage; size_t bytes; };
+static ExtractWs carve_extract(void* base, int B, int A, int rowcap, size_t elt) {
   Carver c(base);
   ExtractWs w;
   w.counts = c.take<int>((size_t)B * A);
   w.offsets = c.take<int>((size_t)B * (A + 1));
+  w.stage = c.take<unsigned char>((size_t)B * A * rowcap * elt);
   w.bytes = c.off;
   return w;
 }
 
-template <typename T, bool FUSED, bool WRITE>
+template <typename T, bool FUSED>
 static int launch_peak_rows(const PeakArgs& a, cudaStream_t st) {
   size_t smem = (size_t)a.R * sizeof(T) + 16;
   if (FUSED) smem += (size_t)(a.cfar.hi - a.cfar.lo + 1) * sizeof(double);
-  int rc = opt_in_smem(peak_rows_kernel<T, FUSED, WRITE>, smem);
+  int rc = opt_in_smem(peak_rows_kernel<T, FUSED>, smem);
   if (rc) return rc;
-  peak_rows_kernel<T, FUSED, WRITE><<<a.rows, ROW_THREADS, smem, st>>>(a);
+  peak_rows_kernel<T, FUSED><<<a.rows, ROW_THREADS, smem, st>>>(a);
   return check_launch();
 }
 
-static int fill_peak(const mmb_extract_params* p, const void* src, PeakArgs& a) {
-  if (!p || !src) return MMB_ERR_NULL_POINTER;
+static int fill_peak(const mmb_extract_params* p, const void* src, PeakArgs& a, bool need_src = true) {
+  if (!p || (need_src && !src)) return MMB_ERR_NULL_POINTER;
   if (p->B <= 0 || p->A <= 0 || p->R <= 1) return MMB_ERR_INVALID_SHAPE;
   if (p->dtype != MMB_F32 && p->dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
   a.mask = nullptr; a.mask_row_stride = p->R;
   a.rows = p->B * p->A; a.A = p->A; a.R = p->R;
   a.res = (float)p->res; a.diff = p->diff ? 1 : 0; a.steep = p->steep_fact;
-  a.counts = nullptr; a.offsets = nullptr; a.ent_val = nullptr; a.ent_row = nullptr; a.cap = 0;
+  a.counts = nullptr; a.stage = nullptr; a.rowcap = p->R;
   if (p->fused) {
     if (p->cfar.B != p->B || p->cfar.A != p->A || p->cfar.R != p->R || p->cfar.dtype != p->dtype)
       return MMB_ERR_INVALID_SHAPE;
-    return fill_cfar(&p->cfar, src, a.cfar);
+    const int rc = fill_cfar(&p->cfar, src, a.cfar);
+    if (rc) return rc;
+  } else {
+    a.mask = src;
   }
-  a.mask = src;
+  int c0, c1;
+  peak_span(a, p->fused != 0, c0, c1);
+  a.rowcap = c1 - c0 > 0 ? c1 - c0 : 1;
   return MMB_OK;
 }
 
@@ -830,9 +851,10 @@ int mmb_cfar_mask(const mmb_cfar_params* p, const void* scan, void* mask, void* 
   return check_launch();
 }
 
-size_t mmb_extract_workspace_bytes(int32_t B, int32_t A) {
-  if (B <= 0 || A <= 0) return 0;
-  return carve_extract(nullptr, B, A).bytes;
+size_t mmb_extract_workspace_bytes(const mmb_extract_params* p) {
+  PeakArgs a;
+  if (fill_peak(p, nullptr, a, false)) return 0;
+  return carve_extract(nullptr, p->B, p->A, a.rowcap, (size_t)(p->dtype == MMB_F64 ? 8 : 4)).bytes;
 }
 
 int mmb_extract_count(const mmb_extract_params* p, const void* mask_or_scan, void* workspace, size_t workspace_bytes,
@@ -842,42 +864,40 @@ int mmb_extract_count(const mmb_extract_params* p, const void* mask_or_scan, voi
   if (rc) return rc;
   if (!workspace || !totals) return MMB_ERR_NULL_POINTER;
   if (reinterpret_cast<uintptr_t>(workspace) % 256) return MMB_ERR_MISALIGNED;
-  ExtractWs w = carve_extract(workspace, p->B, p->A);
+  ExtractWs w = carve_extract(workspace, p->B, p->A, a.rowcap, (size_t)(p->dtype == MMB_F64 ? 8 : 4));
   if (workspace_bytes < w.bytes) return MMB_ERR_WORKSPACE_TOO_SMALL;
-  a.counts = w.counts;
+  a.counts = w.counts; a.stage = w.stage;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (p->dtype == MMB_F32) rc = p->fused ? launch_peak_rows<float, true, false>(a, st) : launch_peak_rows<float, false, false>(a, st);
-  else rc = p->fused ? launch_peak_rows<double, true, false>(a, st) : launch_peak_rows<double, false, false>(a, st);
+  if (p->dtype == MMB_F32) rc = p->fused ? launch_peak_rows<float, true>(a, st) : launch_peak_rows<float, false>(a, st);
+  else rc = p->fused ? launch_peak_rows<double, true>(a, st) : launch_peak_rows<double, false>(a, st);
   if (rc) return rc;
   row_offsets_kernel<<<p->B, 256, 0, st>>>(w.counts, p->A, w.offsets, totals);
   return check_launch();
 }
 
-int mmb_extract_write(const mmb_extract_params* p, const void* mask_or_scan, const void* azimuths, const void* T_ab,
+int mmb_extract_write(const mmb_extract_params* p, const void* azimuths, const void* T_ab,
                       void* workspace, size_t workspace_bytes, int32_t entry_cap, void* ent_val, int32_t* ent_row,
                       int32_t out_cap, void* points_out, void* stream) {
   PeakArgs a;
-  int rc = fill_peak(p, mask_or_scan, a);
+  int rc = fill_peak(p, nullptr, a, false);
   if (rc) return rc;
   if (!workspace || !azimuths || !ent_val || !ent_row || !points_out) return MMB_ERR_NULL_POINTER;
   if (entry_cap <= 0 || out_cap <= 0) return MMB_ERR_INVALID_SHAPE;
   if (reinterpret_cast<uintptr_t>(workspace) % 256) return MMB_ERR_MISALIGNED;
-  ExtractWs w = carve_extract(workspace, p->B, p->A);
+  ExtractWs w = carve_extract(workspace, p->B, p->A, a.rowcap, (size_t)(p->dtype == MMB_F64 ? 8 : 4));
   if (workspace_bytes < w.bytes) return MMB_ERR_WORKSPACE_TOO_SMALL;
-  a.counts = w.counts; a.offsets = w.offsets; a.ent_val = ent_val; a.ent_row = ent_row; a.cap = entry_cap;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (p->dtype == MMB_F32) rc = p->fused ? launch_peak_rows<float, true, true>(a, st) : launch_peak_rows<float, false, true>(a, st);
-  else rc = p->fused ? launch_peak_rows<double, true, true>(a, st) : launch_peak_rows<double, false, true>(a, st);
-  if (rc) return rc;
   dim3 grid((out_cap + 255) / 256, p->B);
   if (p->dtype == MMB_F32)
-    peak_points_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(ent_val), ent_row, w.offsets,
+    peak_points_kernel<float><<<grid, 256, 0, st>>>(static_cast<const float*>(w.stage), a.rowcap, w.offsets,
                                                     static_cast<const float*>(azimuths), static_cast<const float*>(T_ab),
-                                                    p->A, entry_cap, out_cap, static_cast<float*>(points_out));
+                                                    p->A, entry_cap, out_cap, static_cast<float*>(ent_val), ent_row,
+                                                    static_cast<float*>(points_out));
   else
-    peak_points_kernel<double><<<grid, 256, 0, st>>>(static_cast<const double*>(ent_val), ent_row, w.offsets,
+    peak_points_kernel<double><<<grid, 256, 0, st>>>(static_cast<const double*>(w.stage), a.rowcap, w.offsets,
                                                      static_cast<const double*>(azimuths),
                                                      static_cast<const double*>(T_ab), p->A, entry_cap, out_cap,
+                                                     static_cast<double*>(ent_val), ent_row,
                                                      static_cast<double*>(points_out));
   return check_launch();
 }

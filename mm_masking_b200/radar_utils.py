@@ -145,7 +145,7 @@ def _extract(src, p, azimuth_angles, T_ab, out_device):
     Tm = None if T_ab is None else torch.as_tensor(T_ab).detach().to(device=dev, dtype=wdt).contiguous()
     B, A = p.B, p.A
     with torch.cuda.device(dev):
-        ws_bytes = lib.mmb_extract_workspace_bytes(B, A)
+        ws_bytes = lib.mmb_extract_workspace_bytes(p)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         totals = torch.empty(B, dtype=torch.int32, device=dev)
         _capi.check(lib.mmb_extract_count(p, _capi.ptr(src), _capi.ptr(ws), ws_bytes, _capi.ptr(totals),
@@ -157,7 +157,7 @@ def _extract(src, p, azimuth_angles, T_ab, out_device):
         ent_val = torch.empty((B, cap), dtype=wdt, device=dev)
         ent_row = torch.empty((B, cap), dtype=torch.int32, device=dev)
         pts = torch.empty((B, cap // 2, 3), dtype=wdt, device=dev)
-        _capi.check(lib.mmb_extract_write(p, _capi.ptr(src), _capi.ptr(az), _capi.ptr(Tm), _capi.ptr(ws), ws_bytes,
+        _capi.check(lib.mmb_extract_write(p, _capi.ptr(az), _capi.ptr(Tm), _capi.ptr(ws), ws_bytes,
                                           cap, _capi.ptr(ent_val), _capi.ptr(ent_row), cap // 2, _capi.ptr(pts),
                                           _capi.stream_ptr()), "mmb_extract_write")
     out = [pts[b, :tot[b] // 2] for b in range(B)]
