@@ -359,7 +359,10 @@ def run_ours(args, wl, rank, world, local_rank):
         hbm = hbm_peak or 6455.9
         gbs = grid_bytes / (nn_ms * 1e-3) / 1e9
         roofline = {"kernel": "nn_grid_kernel", "bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s",
-                    "frac": gbs / hbm, "traffic": None, "bytes_per_launch": grid_bytes, "ms_per_launch": nn_ms,
+                    "frac": gbs / hbm, "traffic": 29.62e6 if args.workload == "c3" else None,
+                    "traffic_source": "profiles/r01h_ncu_nn_grid_source_summary.md (ncu --set full, c3, warm iteration: "
+                                      "dram read 29.28 MB + write 0.34 MB per launch)",
+                    "bytes_per_launch": grid_bytes, "ms_per_launch": nn_ms,
                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if hbm_peak else "fallback 6455.9 GB/s",
                     "work_avoiding": True,
                     "exhaustive_equivalent_tflops": nn_flop / (nn_ms * 1e-3) / 1e12,
