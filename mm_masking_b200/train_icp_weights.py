@@ -13,6 +13,7 @@ from __future__ import annotations
 import torch
 
 from . import dist as mdist
+from .prefetch import DevicePrefetcher
 from .radar_utils import extract_bev_from_pts
 
 DEFAULT_LOSS_WEIGHTS = {"icp_rot": 1.0, "icp_trans": 1.0, "fft": 0.0, "mask_pts": 1.0, "cfar": 0.0, "num_pts": 0.0}
@@ -88,14 +89,22 @@ def train_step(model, batch, opt, loss_weights=DEFAULT_LOSS_WEIGHTS, device='cud
     return loss.detach(), loss_comp
 
 
+def _staged(iterator, device, prefetch):
+    """with a CUDA device the batches come through `DevicePrefetcher`: batch k+1 uploads on a copy stream
+    under the kernels of batch k, and the `.to(device)` calls of the loop body become no-ops"""
+    if prefetch and torch.device(device).type == 'cuda' and not isinstance(iterator, DevicePrefetcher):
+        return DevicePrefetcher(iterator, device)
+    return iterator
+
+
 def train_policy(model, iterator, opt, loss_weights=DEFAULT_LOSS_WEIGHTS, device='cpu', epoch=None, icp_loss_only_iter=0,
-                 gt_eye=True):
+                 gt_eye=True, prefetch=True):
     """`train_icp_weights.py:22-69`"""
     model.train()
     loss_hist = 0.0
     loss_comp_hist = []
     count = 0
-    for batch in iterator:
+    for batch in _staged(iterator, device, prefetch):
         loss, loss_comp = train_step(model, batch, opt, loss_weights, device, epoch, icp_loss_only_iter, gt_eye)
         loss_hist += loss
         loss_comp_hist.append(loss_comp)
@@ -105,13 +114,14 @@ def train_policy(model, iterator, opt, loss_weights=DEFAULT_LOSS_WEIGHTS, device
     return mean_loss, mean_loss_comp
 
 
-def validate_policy(model, iterator, gt_eye=True, device='cpu', binary=False, neptune_run=None, epoch=None):
+def validate_policy(model, iterator, gt_eye=True, device='cpu', binary=False, neptune_run=None, epoch=None,
+                    prefetch=True):
     """`train_icp_weights.py:71-176` without the Neptune figures."""
     model.eval()
     val_acc = torch.zeros((1, 3), device=device)
     mean_num_pc, max_w, min_w, mean_w, count = 0.0, 0.0, 1000.0, 0.0, 0
     with torch.no_grad():
-        for batch in iterator:
+        for batch in _staged(iterator, device, prefetch):
             batch_T = batch['transforms']
             T_pred, mask, _ = model(batch['loc_data'], batch['map_data'], batch_T['T_ml_init'].to(device), binary=binary)
             mean_num_pc += model.mean_num_pts

@@ -55,3 +55,10 @@ def test_training_and_validation_loss(g, i, gt_eye, monkeypatch):
     np.testing.assert_allclose([gm.sum(), np.abs(gm).sum(), (gm * d["mask"]).sum()], g[tag + "_gmask_sum"], rtol=1e-4, atol=1e-7)
     val = TW.eval_validation_loss(torch.from_numpy(d["T_pred"]), torch.from_numpy(d["T_gt"]), gt_eye=gt_eye).numpy()
     np.testing.assert_allclose(val, g[tag + "_val"], rtol=1e-6)
+
+
+def test_epoch_loops_stage_batches_only_for_cuda_devices():
+    from mm_masking_b200 import train_icp_weights as TW
+    it = [{"a": torch.zeros(2)}]
+    assert TW._staged(it, "cpu", True) is it
+    assert TW._staged(it, "cuda", False) is it

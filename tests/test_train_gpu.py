@@ -37,6 +37,16 @@ def test_training_step_updates_the_unet_and_matches_the_oracle_icp():
     assert any(float(g.abs().max()) > 0 for g in grads)
     assert any(not torch.equal(a, b.detach()) for a, b in zip(before, model.parameters()))
 
+    # the epoch loop: batches come through the DevicePrefetcher (host batches in, same losses out)
+    from mm_masking_b200.prefetch import DevicePrefetcher, pin_batch
+    cpu_batch = {k: {kk: (vv.cpu() if torch.is_tensor(vv) else vv) for kk, vv in v.items()} for k, v in batch.items()}
+    staged = TW._staged([cpu_batch], "cuda", True)
+    assert isinstance(staged, DevicePrefetcher) and TW._staged(staged, "cuda", True) is staged
+    mean_loss, mean_comp = TW.train_policy(model, [pin_batch(cpu_batch), cpu_batch], opt, device="cuda", gt_eye=False)
+    assert torch.isfinite(mean_loss).all() and set(mean_comp) == set(comp)
+
     model.eval()
     val = TW.validate_policy(model, [batch], gt_eye=False, device="cuda")
     assert val[0].shape == (1, 3) and torch.isfinite(val[0]).all()
+    val_host = TW.validate_policy(model, [cpu_batch], gt_eye=False, device="cuda")
+    assert torch.allclose(val_host[0], val[0], atol=1e-6)
