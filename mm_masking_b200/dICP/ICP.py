@@ -27,6 +27,20 @@ from .nn import nn
 _LOSS_KIND = {"huber": _capi.LOSS_HUBER, "cauchy": _capi.LOSS_CAUCHY}
 
 
+def _zeros_block(device, specs):
+    """zero tensors of the given (shape, dtype) list as 256-byte aligned views of one zero-filled buffer"""
+    spans, total = [], 0
+    for shape, dt in specs:
+        count = 1
+        for d in shape:
+            count *= int(d)
+        nbytes = count * torch.empty((), dtype=dt).element_size()
+        spans.append((total, nbytes))
+        total += (nbytes + 255) // 256 * 256
+    flat = torch.zeros(total, dtype=torch.uint8, device=device)
+    return [flat[o:o + nb].view(dt).view(shape) for (o, nb), (shape, dt) in zip(spans, specs)]
+
+
 class _IcpFunction(torch.autograd.Function):
     """source (N,n,3), target (N,m,3|6), T_init (N,4,4), weight (N,n) or None -> T, pc (+ histories)."""
 
@@ -75,13 +89,11 @@ class _IcpFunction(torch.autograd.Function):
             saved = torch.empty(sv_bytes, dtype=torch.uint8, device=dev) if sv_bytes else None
             T_out = torch.empty((N, 4, 4), dtype=dtype, device=dev)
             pc = torch.empty((N, n, 3), dtype=dtype, device=dev)
-            deltas = torch.zeros((N, K, 6), dtype=dtype, device=dev)
-            weights = torch.zeros((N, K, rows), dtype=dtype, device=dev)
-            costs = torch.zeros((N, K), dtype=dtype, device=dev)
-            converged = torch.zeros((N,), dtype=torch.uint8, device=dev)
-            iterations = torch.zeros((N,), dtype=dtype, device=dev)
-            matched = torch.zeros((N,), dtype=dtype, device=dev)
-            iters_done = torch.zeros((1,), dtype=torch.int32, device=dev)
+            # the zero-initialised outputs (rows of iterations that are not executed stay zero) are carved
+            # from ONE zero-filled block: one fill launch instead of seven
+            deltas, weights, costs, converged, iterations, matched, iters_done = _zeros_block(dev, (
+                ((N, K, 6), dtype), ((N, K, rows), dtype), ((N, K), dtype), ((N,), torch.uint8), ((N,), dtype),
+                ((N,), dtype), ((1,), torch.int32)))
             rc = lib.mmb_icp_forward(p, _capi.ptr(src), _capi.ptr(tgt), _capi.ptr(T0), _capi.ptr(w),
                                      _capi.ptr(T_out), _capi.ptr(pc), _capi.ptr(deltas), _capi.ptr(weights),
                                      _capi.ptr(costs), _capi.ptr(converged), _capi.ptr(iterations),
