@@ -393,6 +393,8 @@ def run_ours(args, wl, rank, world, local_rank):
                 "serial_upload_value": world * N / (ms_e2e_serial * 1e-3),
                 "overlap": "H2D of step k+1 on a copy stream under the kernels of step k (DevicePrefetcher); "
                            "K uploads inside the timed region, L2 flush time included"},
+        # kernels of this library inside the two timed regions behind `value` and `e2e` (K steps each); the
+        # serial-upload comparison loop launches the same number again
         "gpu_launches": launches_per_step * args.steps * 2,
         "roofline": roofline,
         "roofline_exhaustive_nn": roofline_brute,
