@@ -101,6 +101,9 @@ class _IcpFunction(torch.autograd.Function):
                                      _capi.ptr(workspace), ws_bytes, _capi.stream_ptr())
             _capi.check(rc, "mmb_icp_forward")
 
+        if cfg.get("record_indices") and saved is not None:
+            # test hook: the correspondences of every executed iteration, (K,N,n) int32 -- the first block of `saved`
+            cfg["indices_out"] = saved[:K * N * n * 4].view(torch.int32).view(K, N, n)
         ctx.params = p
         ctx.has_weight = weight is not None
         ctx.save_for_backward(src, tgt, w if w is not None else src.new_empty(0), saved if saved is not None else src.new_empty(0))
@@ -147,6 +150,8 @@ class ICP:
         self.diff = differentiable
         self.nn_slices = 0          # 0: the library picks the target split of the NN search
         self.nn_backend = _capi.NN_AUTO   # exact cell grid for large maps, brute force otherwise (same indices)
+        self.record_indices = False       # tests: keep the per-iteration correspondences in `last_indices` (needs a grad input)
+        self.last_indices = None
 
         use_gumbel = self.config['dICP']['functionality']['gumbel']
         if use_gumbel:
@@ -193,10 +198,11 @@ class ICP:
                    loss_kind=loss_kind, loss_metric=loss_metric, dim=int(dim),
                    tanh_steepness=self.config['dICP']['parameters']['tanh_steepness'],
                    match_ratio_thresh=self.match_ratio_thresh, nn_slices=self.nn_slices,
-                   nn_backend=self.nn_backend)
+                   nn_backend=self.nn_backend, record_indices=self.record_indices)
         T, pc, deltas, weights, costs, converged, iterations, matched, iters_done = _IcpFunction.apply(
             source.to(dev), target.to(dev), T_init.to(dev), weight_arg, cfg)
 
+        self.last_indices = cfg.get("indices_out")
         if self.const_iter:
             it = int(self.max_iterations)    # every pair runs all iterations (dICP_config.yaml:7): no host sync at all
         else:

@@ -39,6 +39,8 @@ def nearest_index(query: torch.Tensor, target_xyz: torch.Tensor, mode: str = "ex
     """
     if mode == "cdist":
         return torch.argmin(torch.cdist(query, target_xyz, p=2), dim=2)
+    if mode == "kdtree":
+        return nearest_index_kdtree(query, target_xyz)
     N, n, _ = query.shape
     out = torch.empty((N, n), dtype=torch.long)
     for b in range(N):
@@ -47,6 +49,46 @@ def nearest_index(query: torch.Tensor, target_xyz: torch.Tensor, mode: str = "ex
             q = query[b, s:s + chunk]
             d2 = ((q[:, None, :] - t[None, :, :]) ** 2).sum(dim=2)
             out[b, s:s + chunk] = torch.argmin(d2, dim=1)
+    return out
+
+
+_TREES: dict = {}
+
+
+def nearest_index_kdtree(query: torch.Tensor, target_xyz: torch.Tensor, k: int = 8) -> torch.Tensor:
+    """The same answer as mode="exact" at map sizes where the (n, m) distance table is too slow
+    (c3: m = 50 000, c5: m = 200 000): a k-d tree (scipy) proposes the k nearest targets of every
+    query, the squared distances of those k are then evaluated with the expression of mode="exact"
+    and the winner is the lexicographic minimum of (d^2, index).  The proposal is exact unless more
+    than k - 1 targets lie within rounding of the nearest distance (the synthetic maps duplicate
+    1 % of their points pairwise, so k = 8 leaves ample room); when the k-th proposal still ties
+    with the best, the query falls back to the full scan.  `tests/test_oracle_properties_cpu.py`
+    checks it against mode="exact"."""
+    import numpy as np
+    from scipy.spatial import cKDTree
+    N, n, _ = query.shape
+    out = torch.empty((N, n), dtype=torch.long)
+    for b in range(N):
+        t = target_xyz[b].double()
+        q = query[b].double()
+        kk = min(k, t.shape[0])
+        # the map does not move between iterations: keep the tree of the latest few maps
+        key = (target_xyz.data_ptr(), tuple(target_xyz.shape), b, float(t.sum()), float(t[-1].sum()))
+        tree = _TREES.get(key)
+        if tree is None:
+            if len(_TREES) >= 16:
+                _TREES.clear()
+            tree = _TREES[key] = cKDTree(t.numpy())
+        _, cand = tree.query(q.numpy(), k=kk)
+        cand = torch.from_numpy(np.asarray(cand).reshape(n, kk).astype(np.int64))
+        d2 = ((q[:, None, :] - t[cand]) ** 2).sum(dim=2)                     # (n, kk), the "exact" expression
+        best = d2.min(dim=1, keepdim=True).values
+        tie = d2 == best
+        idx = torch.where(tie, cand, torch.full_like(cand, t.shape[0])).min(dim=1).values
+        unsure = tie.all(dim=1) & (kk < t.shape[0])                            # every proposal ties: scan everything
+        for i in torch.nonzero(unsure).flatten().tolist():
+            idx[i] = torch.argmin(((q[i][None, :] - t) ** 2).sum(dim=1))
+        out[b] = idx
     return out
 
 

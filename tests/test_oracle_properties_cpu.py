@@ -146,3 +146,34 @@ def test_kstrongest_keeps_at_most_k_per_azimuth_strongest_first():
     rho = np.hypot(pts[:, 0], pts[:, 1])
     bins = np.rint((rho + 0.31) / res).astype(int)
     assert bins.tolist() == [100, 102, 101, 209, 208, 207, 206, 205, 300, 400]
+
+
+@pytest.mark.parametrize("dim", [2, 3])
+def test_kdtree_nn_mode_equals_exact_mode(dim):
+    """`nn_mode="kdtree"` (the checker used at c3 / c5 map sizes) returns the indices of the exhaustive
+    `nn_mode="exact"`: synthetic map with 1 % duplicated points (exact ties -> lowest index), pad rows, and
+    queries that sit exactly on targets."""
+    from mm_masking_b200 import synth
+    batch = synth.make_icp_batch(N=2, n=400, m=6000, seed=5, three_d=dim == 3)
+    tgt = torch.tensor(batch["target"][:, :, :3], dtype=torch.float64)
+    if dim == 2:
+        tgt = tgt * torch.tensor([1.0, 1.0, 0.0], dtype=torch.float64)
+    g = torch.Generator().manual_seed(3)
+    q = tgt[:, torch.randint(0, 6000, (400,), generator=g)] + 0.3 * torch.randn((2, 400, 3), generator=g, dtype=torch.float64)
+    q[:, :40] = tgt[:, torch.randint(0, 6000, (40,), generator=g)]            # distance exactly 0, some duplicated
+    q[:, 40:80] += 30.0 * torch.randn((2, 40, 3), generator=g, dtype=torch.float64)   # far from everything
+    if dim == 2:
+        q[:, :, 2] = 0.0
+    tgt[1, 100:110] = tgt[1, 99]                                              # an 11-fold tie: the full-scan fallback
+    q[1, 0] = tgt[1, 99]
+    a = O.nearest_index(q, tgt, "exact")
+    b = O.nearest_index(q, tgt, "kdtree")
+    assert torch.equal(a, b)
+    assert int(b[1, 0]) <= 99
+
+
+def test_kdtree_mode_gives_the_same_icp_run():
+    src, tgt, T0, w = _scene()
+    a = O.dicp(src, tgt, T0, w, return_indices=True, **KW)
+    b = O.dicp(src, tgt, T0, w, return_indices=True, nn_mode="kdtree", **KW)
+    assert torch.equal(a["indices"], b["indices"]) and torch.equal(a["T"], b["T"])
