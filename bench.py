@@ -115,18 +115,100 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------
 # CPU reference arm / cpu_baseline (oracle port; the one place bench.py executes oracle/)
 # ---------------------------------------------------------------------------------------------
-def cpu_reference_step(batch, wl, pairs):
-    """fwd+bwd of the reference algorithm on `pairs` pairs, on the host cores.  Returns seconds."""
+REF_DIR = os.path.join(ROOT, "oracle", "_ref", "dicp_ref")
+
+
+def reference_kind():
+    """"reference": the UNMODIFIED dICP package copied by oracle/Makefile into the git-ignored oracle/_ref/
+    (it travels to the GPU box like the built .so); "port": the oracle restatement, when that copy is absent."""
+    return "reference" if os.path.exists(os.path.join(REF_DIR, "dICP", "ICP.py")) else "port"
+
+
+_REF_ICP = {}
+
+
+def _reference_icp(iters):
+    """the reference's own `dICP.ICP.ICP` (external/dICP/dICP/ICP.py:14-46), constructed as
+    `mm_masking/icp_weight_policy.py:54` does; `const_iter` is the reference's own config switch
+    (config/dICP_config.yaml:7), set on the instance so that every pair does all iterations."""
+    if iters not in _REF_ICP:
+        from oracle import ref_loader
+        ref_loader._stub_matplotlib()              # the reference imports matplotlib at module top, unused on the path
+        if REF_DIR not in sys.path:
+            sys.path.insert(0, REF_DIR)
+        from dICP.ICP import ICP as RefICP
+        alg = RefICP(icp_type="pt2pl", differentiable=True, max_iterations=iters, tolerance=1e-5)
+        alg.const_iter = True
+        _REF_ICP[iters] = alg
+    return _REF_ICP[iters]
+
+
+def cpu_reference_step(batch, wl, pairs, chunk=8):
+    """fwd+bwd of the reference on `pairs` pairs, on the host cores, in chunks of <= 8 pairs (its (N,n,m)
+    distance tensor is 0.4 GB per pair at c3).  Returns seconds."""
+    import torch
+    kind = reference_kind()
+    secs = 0.0
+    for s0 in range(0, pairs, chunk):
+        t = lambda a: torch.tensor(a[s0:min(pairs, s0 + chunk)])
+        src, tgt, T0 = t(batch["source"]), t(batch["target"]), t(batch["T_init"])
+        w = t(batch["weight"]).requires_grad_(True)
+        t0 = time.perf_counter()
+        if kind == "reference":
+            out = _reference_icp(wl["iters"]).icp(src, tgt, T0, weight=w, trim_dist=5.0,
+                                                  loss_fn={"name": "cauchy", "metric": 1.0}, dim=wl["dim"])
+        else:
+            from oracle import dicp_oracle as O
+            out = O.dicp(src, tgt, T0, w, icp_type="pt2pl", max_iterations=wl["iters"], tolerance=1e-5,
+                         differentiable=True, trim_dist=5.0, loss_fn={"name": "cauchy", "metric": 1.0},
+                         dim=wl["dim"], const_iter=True, nn_mode="cdist")
+        out["T"].sum().backward()
+        secs += time.perf_counter() - t0
+    return secs
+
+
+def reference_sample_text(kind, pairs, iters):
+    what = ("unmodified reference dICP.ICP.icp (oracle/_ref/dicp_ref, torch CPU)" if kind == "reference"
+            else "oracle port (torch.cdist+argmin NN)")
+    return f"{pairs} pair(s) x {iters} it fwd+bwd per step, fp32, {what}"
+
+
+def parity_check(alg, call, wl, batch, dev_tensors, pairs=2):
+    """The timed call once more with the per-iteration correspondences recorded, against the CPU oracle
+    (fp64, exhaustive-search semantics of `external/dICP/dICP/nn.py:32-38` on k-d tree proposals) on the first
+    `pairs` pairs of the very batch that was timed.  BASELINE.json tolerances: indices bit-exact, pose 1e-5 m /
+    1e-6 rad, d/d weight 1e-4 relative."""
+    import numpy as np
     import torch
     from oracle import dicp_oracle as O
-    t = lambda a: torch.tensor(a[:pairs])
-    w = t(batch["weight"]).requires_grad_(True)
-    t0 = time.perf_counter()
-    out = O.dicp(t(batch["source"]), t(batch["target"]), t(batch["T_init"]), w, icp_type="pt2pl",
-                 max_iterations=wl["iters"], tolerance=1e-5, differentiable=True, trim_dist=5.0,
-                 loss_fn={"name": "cauchy", "metric": 1.0}, dim=wl["dim"], const_iter=True, nn_mode="cdist")
+    d_src, d_tgt, d_T0, d_w = dev_tensors
+    w = d_w.detach().clone().requires_grad_(True)
+    alg.record_indices = True
+    out = alg.icp(d_src, d_tgt, d_T0, weight=w, **call)
     out["T"].sum().backward()
-    return time.perf_counter() - t0
+    idx = alg.last_indices[:, :pairs].cpu().numpy().astype(np.int64)
+    alg.record_indices = False
+    T = out["T"][:pairs].detach().double().cpu().numpy()
+    g = w.grad[:pairs].double().cpu()
+    t64 = lambda a: torch.tensor(np.asarray(a[:pairs], dtype=np.float64))
+    w_ref = t64(batch["weight"]).requires_grad_(True)
+    ref = O.dicp(t64(batch["source"]), t64(batch["target"]), t64(batch["T_init"]), w_ref, icp_type="pt2pl",
+                 max_iterations=wl["iters"], tolerance=1e-5, differentiable=True, trim_dist=5.0,
+                 loss_fn={"name": "cauchy", "metric": 1.0}, dim=wl["dim"], const_iter=True, nn_mode="kdtree",
+                 return_indices=True)
+    ref["T"].sum().backward()
+    T_ref = ref["T"].detach().numpy()
+    dT = float(np.abs(T[:, :3, 3] - T_ref[:, :3, 3]).max())
+    dR = np.einsum("bij,bkj->bik", T[:, :3, :3], T_ref[:, :3, :3])
+    sk = np.stack([dR[:, 2, 1] - dR[:, 1, 2], dR[:, 0, 2] - dR[:, 2, 0], dR[:, 1, 0] - dR[:, 0, 1]], 1) / 2
+    dang = float(np.linalg.norm(sk, axis=1).max())
+    scale = max(float(w_ref.grad.abs().max()), 1e-30)
+    dgrad = float((g - w_ref.grad).abs().max()) / scale
+    mism = int((idx != ref["indices"].numpy()).sum())
+    ok = mism == 0 and dT < 1e-5 and dang < 1e-6 and dgrad < 1e-4
+    return {"pairs": pairs, "iterations": int(idx.shape[0]), "idx_mismatch": mism, "idx_compared": int(idx.size),
+            "dT_max": dT, "dR_max": dang, "dgrad_rel": dgrad, "ok": bool(ok),
+            "against": "oracle/dicp_oracle.py fp64, nn_mode=kdtree (exhaustive-search semantics), same batch"}
 
 
 def run_reference(args, wl, rank, world):
@@ -143,14 +225,15 @@ def run_reference(args, wl, rank, world):
     secs = [cpu_reference_step(batch, wl, pairs) for _ in range(args.steps)]
     total = sum(secs)
     value = pairs * args.steps / total
-    sample = f"{pairs} pair(s) x {wl['iters']} it fwd+bwd per step, {args.steps} steps, fp32, torch.cdist+argmin NN"
+    kind = reference_kind()
+    sample = reference_sample_text(kind, pairs, wl["iters"]) + f", {args.steps} steps"
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload + ": " + wl["desc"], "pairs_per_step": pairs, "n": wl["n"], "m": wl["m"],
                    "iterations": wl["iters"], "dim": wl["dim"]},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -270,6 +353,8 @@ def run_ours(args, wl, rank, world, local_rank):
             dist.destroy_process_group()
         return
 
+    parity = parity_check(alg, call, wl, batch, (d_src, d_tgt, d_T0, d_w), pairs=min(2, N))
+
     # ---- roofline of the dominant kernel: per-class CUDA-event timing of the same forward -----
     NC = _capi.PROFILE_CLASSES
     f32 = dict(dtype=torch.float32, device=dev)
@@ -342,8 +427,9 @@ def run_ours(args, wl, rank, world, local_rank):
         pairs = max(1, min(N, args.ref_pairs))
         cpu_reference_step(batch, wl, 1)                     # warm-up (thread pool, allocator)
         secs = cpu_reference_step(batch, wl, pairs)
-        cpu = {"value": pairs / secs, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"{pairs} pair(s) of this workload x {K} it fwd+bwd, fp32, torch.cdist+argmin NN, {secs:.1f} s"}
+        kind = reference_kind()
+        cpu = {"value": pairs / secs, "unit": UNIT, "cores": cores, "kind": kind,
+               "sample": reference_sample_text(kind, pairs, K) + f", one step of {secs:.1f} s"}
 
     peak_src = ("mmb_fp32_probe in this run (max of FFMA and FFMA2 chains); "
                 "MEASURED_PEAKS.json has no CUDA-core FP32 entry")
@@ -399,11 +485,15 @@ def run_ours(args, wl, rank, world, local_rank):
         "roofline": roofline,
         "roofline_exhaustive_nn": roofline_brute,
         "cpu_baseline": cpu,
+        "parity": parity,
         "clocks": clocks,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    if not parity["ok"]:
+        print("bench.py: PARITY FAILED " + json.dumps(parity), file=sys.stderr, flush=True)
+        sys.exit(3)
 
 
 def main():
@@ -413,13 +503,16 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
-    ap.add_argument("--ref-pairs", type=int, default=2, help="pairs per CPU-reference step (bounded sample)")
+    ap.add_argument("--ref-pairs", type=int, default=0,
+                    help="pairs per CPU-reference step (bounded sample); 0 = 8 at c3 (BASELINE.md section 3), 1 at c5")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--nn-backend", default="auto", choices=sorted(NN_BACKENDS),
                     help="nearest-neighbour backend: exact cell grid (auto for m >= 8192) or brute force; same indices")
     ap.add_argument("--nn-slices", type=int, default=0, help="tuning: target slices per query tile (0 = library default)")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
+    if args.ref_pairs <= 0:
+        args.ref_pairs = 1 if wl["m"] > 100000 else min(8, wl["N"])
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
