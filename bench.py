@@ -53,8 +53,40 @@ WORKLOADS = {
 }
 METRIC = "icp_pairs_per_sec_fwd_bwd"
 UNIT = "pairs/s"
-NN_BACKENDS = {"auto": 0, "brute": 1, "grid": 2}
+NN_BACKENDS = {"auto": 0, "brute": 1, "grid": 2, "rows": 3}
 FLOP_PER_PAIR = 8          # 3 sub, 3 mul, 2 add: the distance `torch.cdist` evaluates
+
+
+def kernel_source_sha():
+    """sha256 (first 16 hex) over the CUDA sources: the key that ties an ncu capture in profiles/traffic.json to
+    the binary that is being timed"""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "mm_masking_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh")):
+            h.update(open(os.path.join(d, f), "rb").read())
+    return h.hexdigest()[:16]
+
+
+def traffic_lookup(kernel, workload):
+    """DRAM bytes per launch of `kernel` at `workload` from the committed ncu captures (profiles/traffic.json,
+    written by profiles/ncu_summarise.py).  Returns (bytes or None, info dict)."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    sha = kernel_source_sha()
+    if not os.path.exists(path):
+        return None, {"traffic_stale": True, "traffic_source": "profiles/traffic.json missing"}
+    best = None
+    for e in json.load(open(path)).get("entries", []):
+        if e.get("kernel") == kernel and e.get("workload") == workload:
+            if best is None or e.get("source_sha") == sha:
+                best = e
+    if best is None:
+        return None, {"traffic_stale": True, "traffic_source": f"no ncu capture of {kernel} at {workload} in profiles/traffic.json"}
+    if best.get("source_sha") != sha:
+        return None, {"traffic_stale": True, "traffic_source": best.get("capture"), "traffic_capture_sha": best.get("source_sha"),
+                      "source_sha": sha, "traffic_of_stale_capture": best.get("dram_bytes_per_launch")}
+    return best.get("dram_bytes_per_launch"), {"traffic_stale": False, "traffic_source": best.get("capture"), "source_sha": sha}
 
 
 def make_batch(wl, seed):
@@ -313,28 +345,38 @@ def run_ours(args, wl, rank, world, local_rank):
     if sampler:
         sampler.start()
         time.sleep(0.3)
+    launches0 = lib.mmb_launch_count()
     ms_res, t0, t1 = timed(step_resident, args.steps, args.warmup)
+    launches_resident = lib.mmb_launch_count() - launches0          # includes the W warm-up steps
     # e2e: the same call fed from pinned HOST tensors through the package's DevicePrefetcher (what
     # a user's loop does): every step uploads its own source/target/T_init/weight (no reuse across
     # steps; the upload of step k+1 runs on a copy stream under the kernels of step k) and reads T
     # and d/d weight back.  ONE event pair around all K steps, L2 flushes included, so nothing that
     # happens between steps escapes the clock.
     e2e_warm = max(2, args.warmup // 2)
-    pre = DevicePrefetcher((host for _ in range(e2e_warm + args.steps + 1)), dev)
+    pre = DevicePrefetcher((host for _ in range(e2e_warm + args.steps * max(1, args.e2e_repeats) + 1)), dev)
     for _ in range(e2e_warm):
         step_e2e(next(pre))
     barrier()
     up0 = pre.bytes_uploaded
-    ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ea.record()
-    for _ in range(args.steps):
-        flush.fill_(1)
-        step_e2e(next(pre))
-    eb.record()
-    barrier()
+    launches1 = lib.mmb_launch_count()
+    # >= 3 repeats of the K-step loop, median reported (20 steps are ~25 ms: too short for one sample of a
+    # loop whose uploads overlap the kernels)
+    e2e_ms = []
+    for rep in range(max(1, args.e2e_repeats)):
+        ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ea.record()
+        for _ in range(args.steps):
+            flush.fill_(1)
+            step_e2e(next(pre))
+        eb.record()
+        barrier()
+        e2e_ms.append(mdist.max_over_ranks(ea.elapsed_time(eb), device=dev) / args.steps)
     t1 = time.time()
-    h2d_per_step = (pre.bytes_uploaded - up0) // args.steps
-    ms_e2e = mdist.max_over_ranks(ea.elapsed_time(eb), device=dev) / args.steps
+    launches_e2e = lib.mmb_launch_count() - launches1
+    h2d_per_step = (pre.bytes_uploaded - up0) // (args.steps * len(e2e_ms))
+    ms_e2e = sorted(e2e_ms)[len(e2e_ms) // 2]
+    ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     # for comparison: the reference's loop shape, upload on the compute stream in front of each call
     ea.record()
     for _ in range(args.steps):
@@ -394,8 +436,14 @@ def run_ours(args, wl, rank, world, local_rank):
                     fwd_ms=sum(acc_ms) / reps, nn_share=acc_ms[0] / max(sum(acc_ms), 1e-9),
                     bound_ms=acc_ms[3] / reps, build_ms=acc_ms[4] / reps, other_ms=acc_ms[2] / reps)
 
-    use_grid = NN_BACKENDS[args.nn_backend] == 2 or (NN_BACKENDS[args.nn_backend] == 0 and m >= 8192)
-    prof = profile_forward(NN_BACKENDS[args.nn_backend])
+    backend_id = NN_BACKENDS[args.nn_backend]
+    mode = "brute"
+    if backend_id == 2:
+        mode = "grid"
+    elif backend_id == 3 or (backend_id == 0 and m >= 8192):
+        mode = "rows"
+    use_grid = mode != "brute"
+    prof = profile_forward(backend_id)
     prof_brute = profile_forward(1) if use_grid else prof       # the exhaustive kernel, same data, same run
     nn_ms, step_ms, fwd_ms = prof["nn_ms"], prof["step_ms"], prof["fwd_ms"]
 
@@ -433,37 +481,43 @@ def run_ours(args, wl, rank, world, local_rank):
 
     peak_src = ("mmb_fp32_probe in this run (max of FFMA and FFMA2 chains); "
                 "MEASURED_PEAKS.json has no CUDA-core FP32 entry")
+    tr_b, tr_b_info = traffic_lookup("nn_search_kernel", args.workload)
     roofline_brute = {"kernel": "nn_search_kernel (--nn-backend brute)", "bound": "fp32", "achieved": brute_tf,
-                      "peak": peak_tf, "unit": "TFLOP/s", "frac": brute_tf / peak_tf,
-                      "traffic": 42.0e6 if args.workload == "c3" else None, "traffic_source": "profiles/r01b_ncu_c3_summary.md (ncu --set full, c3, per launch)",
+                      "peak": peak_tf, "unit": "TFLOP/s", "frac": brute_tf / peak_tf, "traffic": tr_b, **tr_b_info,
                       "flop_per_launch": nn_flop, "ms_per_launch": prof_brute["nn_ms"], "peak_source": peak_src,
-                      "peak_detail": peak, "share_of_forward": prof_brute["nn_share"], "forward_ms": prof_brute["fwd_ms"]}
+                      "peak_detail": peak, "share_of_forward": prof_brute["nn_share"], "forward_ms": prof_brute["fwd_ms"],
+                      "note": "frac counts the 8 flop/pair of the reference's distance; the expansion form executes 4 (dim 2), "
+                              "so the FMA pipe itself is ~half as busy as frac says"}
     if use_grid:
-        # cell-grid search: HBM/L2-gather bound.  Algorithmic bytes per launch: per pair
-        # n x (12 B source + 4 B previous index + 12 B result) + m x 16 B sorted copy + the cell table.
-        grid_bytes = N * (n * 28 + m * 16 + (65536 + 8) * 4)
+        # cell-grid search: HBM/L2-gather bound.  Algorithmic bytes per launch, per pair (DESIGN.md sections 3b, 3c):
+        #   grid (search only): n x (12 B source + 4 B previous index + 12 B result) + m x 16 B sorted copy + the start table
+        #   rows (search + step fused): n x (12 source + 4 previous index + 4 index + 4 index history + 24 matched row
+        #                                    + 4 prior weight + 4 weight history) + m x 16 B + the start table
+        per_query = 56 if mode == "rows" else 28
+        kname = "icp_rows_kernel" if mode == "rows" else "nn_grid_kernel"
+        grid_bytes = N * (n * per_query + m * 16 + (65536 + 8) * 4)
         hbm = hbm_peak or 6455.9
         gbs = grid_bytes / (nn_ms * 1e-3) / 1e9
-        roofline = {"kernel": "nn_grid_kernel", "bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s",
-                    "frac": gbs / hbm, "traffic": 29.62e6 if args.workload == "c3" else None,
-                    "traffic_source": "profiles/r01h_ncu_nn_grid_source_summary.md (ncu --set full, c3, warm iteration: "
-                                      "dram read 29.28 MB + write 0.34 MB per launch)",
+        tr, tr_info = traffic_lookup(kname, args.workload)
+        roofline = {"kernel": kname, "bound": "hbm", "achieved": gbs, "peak": hbm, "unit": "GB/s",
+                    "frac": gbs / hbm, "traffic": tr, **tr_info,
                     "bytes_per_launch": grid_bytes, "ms_per_launch": nn_ms,
                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if hbm_peak else "fallback 6455.9 GB/s",
                     "work_avoiding": True,
                     "exhaustive_equivalent_tflops": nn_flop / (nn_ms * 1e-3) / 1e12,
                     "note": "exact cell-grid search: same indices as the exhaustive kernel with ~1e-3 of its distance "
                             "evaluations; latency/issue-bound gathers from L2, not at the HBM roofline; "
-                            "roofline_exhaustive_nn is the compute-bound kernel on the same data in the same run",
+                            "roofline_exhaustive_nn is the compute-bound kernel on the same data in the same run"
+                            + ("; this kernel also evaluates the residual rows, the normal equations and the solve "
+                               "(no separate step kernel)" if mode == "rows" else ""),
                     "share_of_forward": prof["nn_share"], "forward_ms": fwd_ms,
-                    "step_kernel_ms_per_launch": step_ms, "grid_build_ms": prof["build_ms"],
-                    "nn_backend": args.nn_backend}
+                    "step_kernel_ms_per_launch": step_ms if mode == "grid" else None, "grid_build_ms": prof["build_ms"],
+                    "nn_backend": mode}
     else:
         roofline = dict(roofline_brute, kernel="nn_search_kernel", step_kernel_ms_per_launch=step_ms,
                         bound_pass_ms=prof["bound_ms"], nn_backend=args.nn_backend)
 
     # ours only: brute = init, pack, sub-pack, bound pass; grid = init, geometry, count, scan, scatter
-    launches_per_step = ((5 if use_grid else 4) + 2 * K + 1) + 1      # + K x (nn, step), finish; backward
     h2d = sum(host[k].numel() * 4 for k in host)
     d2h = out_T.numel() * 4 + out_gw.numel() * 4
     line = {
@@ -477,11 +531,13 @@ def run_ours(args, wl, rank, world, local_rank):
         "e2e": {"value": world * N / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": h2d_per_step, "d2h_bytes_per_step": d2h,
                 "serial_upload_value": world * N / (ms_e2e_serial * 1e-3),
+                "repeats_ms_per_step": e2e_ms,
                 "overlap": "H2D of step k+1 on a copy stream under the kernels of step k (DevicePrefetcher); "
                            "K uploads inside the timed region, L2 flush time included"},
-        # kernels of this library inside the two timed regions behind `value` and `e2e` (K steps each); the
-        # serial-upload comparison loop launches the same number again
-        "gpu_launches": launches_per_step * args.steps * 2,
+        # kernels of this library launched inside the two timed regions behind `value` and `e2e`, COUNTED by the
+        # library itself (mmb_launch_count differenced around the regions; warm-up steps excluded pro rata)
+        "gpu_launches": int(launches_resident * args.steps // (args.steps + args.warmup) + launches_e2e),
+        "gpu_launches_per_step": launches_resident // (args.steps + args.warmup),
         "roofline": roofline,
         "roofline_exhaustive_nn": roofline_brute,
         "cpu_baseline": cpu,
@@ -506,6 +562,7 @@ def main():
     ap.add_argument("--ref-pairs", type=int, default=0,
                     help="pairs per CPU-reference step (bounded sample); 0 = 8 at c3 (BASELINE.md section 3), 1 at c5")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-repeats", type=int, default=3, help="repeats of the K-step end-to-end loop (median reported)")
     ap.add_argument("--nn-backend", default="auto", choices=sorted(NN_BACKENDS),
                     help="nearest-neighbour backend: exact cell grid (auto for m >= 8192) or brute force; same indices")
     ap.add_argument("--nn-slices", type=int, default=0, help="tuning: target slices per query tile (0 = library default)")

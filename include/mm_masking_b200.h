@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define MMB_ABI_VERSION 3
+#define MMB_ABI_VERSION 4
 
 typedef enum mmb_status {
   MMB_OK = 0,
@@ -38,14 +38,20 @@ enum { MMB_PT2PL = 0, MMB_PT2PT = 1 };
 enum { MMB_LOSS_NONE = 0, MMB_LOSS_HUBER = 1, MMB_LOSS_CAUCHY = 2 };
 /* Nearest-neighbour backend.  Both return the same indices (exact squared differences, lowest
  * index on ties); BRUTE evaluates all n*m pairs like nn.py:32, GRID visits only the cells that can
- * hold the neighbour.  AUTO: GRID when m >= 8192. */
-enum { MMB_NN_AUTO = 0, MMB_NN_BRUTE = 1, MMB_NN_GRID = 2 };
+ * hold the neighbour (Morton-ordered cells, 3 x 3 blocks of a quadtree level, separate step kernel), ROWS
+ * covers the disc of the current bound row by row on a row-major cell grid and evaluates the residual rows,
+ * the normal equations and the solve in the same launch (one launch per iteration).  AUTO: ROWS when
+ * m >= 8192, BRUTE below. */
+enum { MMB_NN_AUTO = 0, MMB_NN_BRUTE = 1, MMB_NN_GRID = 2, MMB_NN_ROWS = 3 };
 #define MMB_PROFILE_CLASSES 8
 
 int mmb_abi_version(void);
 const char* mmb_status_string(int status);
 /* cudaGetLastError text of the most recent MMB_ERR_CUDA on this thread ("" if none). */
 const char* mmb_last_cuda_error(void);
+/* Number of kernels this library has launched in the calling process so far (every launch site counts once).
+ * Measurement aid: bench.py differences it around its timed regions for `gpu_launches`. */
+long long mmb_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------
  * Weighted differentiable ICP.

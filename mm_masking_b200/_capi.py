@@ -15,7 +15,7 @@ LIB_PATH = os.environ.get("MMB_LIBRARY") or os.path.join(_HERE, "libmm_masking_b
 F32, F64 = 0, 1
 PT2PL, PT2PT = 0, 1
 LOSS_NONE, LOSS_HUBER, LOSS_CAUCHY = 0, 1, 2
-NN_AUTO, NN_BRUTE, NN_GRID = 0, 1, 2
+NN_AUTO, NN_BRUTE, NN_GRID, NN_ROWS = 0, 1, 2, 3
 PROFILE_CLASSES = 8
 
 
@@ -59,6 +59,7 @@ SIGNATURES = {
     "mmb_abi_version": (C.c_int, []),
     "mmb_status_string": (C.c_char_p, [C.c_int]),
     "mmb_last_cuda_error": (C.c_char_p, []),
+    "mmb_launch_count": (C.c_longlong, []),
     "mmb_icp_workspace_bytes": (C.c_size_t, [C.POINTER(IcpParams)]),
     "mmb_icp_saved_bytes": (C.c_size_t, [C.POINTER(IcpParams)]),
     "mmb_icp_forward": (C.c_int, [C.POINTER(IcpParams)] + [_P] * 15 + [C.c_size_t, _P]),
@@ -107,7 +108,7 @@ def load_library(path: str | None = None):
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)
         fn.restype, fn.argtypes = res, args
-    if lib.mmb_abi_version() != 3:
+    if lib.mmb_abi_version() != 4:
         raise MmbError("libmm_masking_b200.so ABI version mismatch")
     _lib = lib
     return lib

@@ -29,6 +29,7 @@ __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.lau
 namespace mmb {
 
 static thread_local char g_last_cuda_error[256] = "";
+std::atomic<long long> g_launch_count{0};      // kernels of this library launched by this process (mmb_launch_count)
 void set_last_cuda_error(cudaError_t e) {
   const char* s = cudaGetErrorString(e);
   int i = 0;
@@ -61,13 +62,18 @@ constexpr double GRID_MARGIN_REL = 0.125;       // ... plus this fraction of its
 constexpr int GRID_OUTSIDE = GRID_CELLS;        // key of the targets that lie outside the grid
 constexpr int GRIDNN_THREADS = 256;
 constexpr int GRID_STRIDE = GRID_CELLS + 8;     // ints per pair in the start / cursor tables (16-byte aligned rows)
+#ifndef MMB_ROWS_QW
+#define MMB_ROWS_QW 4
+#endif
+constexpr int GRID_ROWS_QB_HOST = 8 * MMB_ROWS_QW;   // queries per block of icp_rows_kernel (8 warps x MMB_ROWS_QW)
 
 struct IcpPlan {
   int N, n, m, mp, R;            // mp: m rounded up to NN_TILE; R residual rows
   int qtiles, S, tiles_per_slice;
   int D;                         // solved DoF
   int sub_stride, msub, msp, S_sub, sub_tiles_per_slice;   // strided subsample (0 = no bound pass)
-  int grid;                      // 1: cell-grid search, 0: brute force
+  int grid;                      // 0: brute force, 1: Morton cell grid (nn_grid_kernel), 2: row-major cell grid fused with the step (icp_rows_kernel)
+  int nblk;                      // grid == 2: blocks (= partial-sum slots) per pair
   int f64;                       // element type of the sorted copy
 };
 
@@ -90,7 +96,8 @@ static IcpPlan make_plan(int N, int n, int m, int icp_type, int dim, int nn_slic
   IcpPlan pl;
   pl.N = N; pl.n = n; pl.m = m;
   pl.f64 = dtype == MMB_F64 ? 1 : 0;
-  pl.grid = nn_backend == MMB_NN_GRID || (nn_backend == MMB_NN_AUTO && m >= GRID_MIN_M) ? 1 : 0;
+  pl.grid = nn_backend == MMB_NN_GRID ? 1 : (nn_backend == MMB_NN_ROWS || (nn_backend == MMB_NN_AUTO && m >= GRID_MIN_M) ? 2 : 0);
+  pl.nblk = (n + GRID_ROWS_QB_HOST - 1) / GRID_ROWS_QB_HOST;
   pl.mp = (int)align_up((size_t)m, NN_TILE);
   pl.R = icp_type == MMB_PT2PT ? 3 * n : n;
   pl.qtiles = (n + NN_QB - 1) / NN_QB;
@@ -139,6 +146,10 @@ struct IcpWorkspace {
   int* cell_cursor;              // (N, GRID_CELLS+1) counts, then scatter cursors
   int* keys;                     // (N,m) Morton cell of every target (GRID_OUTSIDE: not in the grid)
   void* sorted;                  // (N,m) targets in cell order: float4 / 4 doubles (x, y, z, original index)
+  // row-major backend only
+  int* ranks;                    // (N,m) arrival rank of every target within its cell (counting pass) -> scatter without atomics
+  double* partials;              // (N, nblk, 32) per-block partial sums of the normal equations
+  int* arrive;                   // (N) blocks of the pair that have parked their partials in this launch
   size_t bytes;
 };
 
@@ -169,6 +180,9 @@ static IcpWorkspace carve_workspace(void* base, const IcpPlan& pl) {
   w.cell_cursor = c.take<int>(NG * GRID_STRIDE);
   w.keys = c.take<int>(Nm);
   w.sorted = pl.f64 ? static_cast<void*>(c.take<double>(Nm * 4)) : static_cast<void*>(c.take<float>(Nm * 4));
+  w.ranks = c.take<int>(pl.grid == 2 ? Nm : 0);
+  w.partials = c.take<double>(pl.grid == 2 ? (size_t)pl.N * pl.nblk * 32 : 0);
+  w.arrive = c.take<int>(pl.grid == 2 ? pl.N : 0);
   w.bytes = c.off;
   return w;
 }
@@ -214,6 +228,7 @@ __global__ void init_state_kernel(const T* __restrict__ T_init, IcpWorkspace w, 
   }
   w.prev_cost[b] = 0.0; w.num_iters[b] = 0.0; w.match_ratio[b] = 0.0;
   w.frozen[b] = 0; w.conv[b] = 0; w.n_matched[b] = 0; w.n_start[b] = 0;
+  if (w.arrive) w.arrive[b] = 0;
 }
 
 __global__ void identity_pose_kernel(double* pose, int N) {
@@ -610,17 +625,27 @@ __global__ void grid_geom_kernel(const T* __restrict__ source, const double* __r
   }
 }
 
+// row-major key of a point given its cell coordinates (doubles), or GRID_OUTSIDE
+__device__ __forceinline__ int grid_key_rows(double fx, double fy) {
+  if (!(fx >= 0.0 && fx < (double)GRID_G && fy >= 0.0 && fy < (double)GRID_G)) return GRID_OUTSIDE;
+  return (int)fy * GRID_G + (int)fx;
+}
+
+// ranks == nullptr: Morton keys (nn_grid_kernel).  ranks != nullptr: row-major keys (icp_rows_kernel) and the
+// arrival rank of the target within its cell, so that the scatter needs no second atomic pass.
 template <typename T>
 __global__ void grid_count_kernel(const T* __restrict__ target, int cols, int N, int m, const double* __restrict__ geom,
-                                  int* __restrict__ keys, int* __restrict__ counts) {
+                                  int* __restrict__ keys, int* __restrict__ counts, int* __restrict__ ranks) {
   const size_t total = (size_t)N * m;
   for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (size_t)gridDim.x * blockDim.x) {
     const int b = (int)(g / m);
     const T* row = target + g * cols;
     const double* gm = geom + (size_t)b * 4;
-    const int key = grid_key(((double)row[0] - gm[0]) * gm[2], ((double)row[1] - gm[1]) * gm[2]);
+    const double fx = ((double)row[0] - gm[0]) * gm[2], fy = ((double)row[1] - gm[1]) * gm[2];
+    const int key = ranks ? grid_key_rows(fx, fy) : grid_key(fx, fy);
     keys[g] = key;
-    atomicAdd(&counts[(size_t)b * GRID_STRIDE + key], 1);
+    const int r = atomicAdd(&counts[(size_t)b * GRID_STRIDE + key], 1);
+    if (ranks) ranks[g] = r;
   }
 }
 
@@ -682,6 +707,22 @@ __global__ void grid_scatter_kernel(const T* __restrict__ target, int cols, int 
     const int b = (int)(g / m), j = (int)(g % m);
     const T* row = target + g * cols;
     const int pos = atomicAdd(&cursor[(size_t)b * GRID_STRIDE + keys[g]], 1);
+    SortedPoint<T> sp; sp.x = row[0]; sp.y = row[1]; sp.z = row[2]; sp.j = j;
+    sorted[(size_t)b * m + pos] = sp;
+  }
+}
+
+// scatter by (cell start + rank from the counting pass): no atomics.  The order inside a cell is the arrival
+// order of the counting pass; the search result does not depend on it (ties go to the lowest ORIGINAL index).
+template <typename T>
+__global__ void grid_scatter_ranked_kernel(const T* __restrict__ target, int cols, int N, int m,
+                                           const int* __restrict__ keys, const int* __restrict__ ranks,
+                                           const int* __restrict__ start, SortedPoint<T>* __restrict__ sorted) {
+  const size_t total = (size_t)N * m;
+  for (size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x; g < total; g += (size_t)gridDim.x * blockDim.x) {
+    const int b = (int)(g / m), j = (int)(g % m);
+    const T* row = target + g * cols;
+    const int pos = __ldg(start + (size_t)b * GRID_STRIDE + keys[g]) + ranks[g];
     SortedPoint<T> sp; sp.x = row[0]; sp.y = row[1]; sp.z = row[2]; sp.j = j;
     sorted[(size_t)b * m + pos] = sp;
   }
@@ -1190,6 +1231,412 @@ __global__ void __launch_bounds__(STEP_THREADS) icp_step_kernel(StepArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------
+// K3c + K4 + K5 fused: exact nearest neighbour on a ROW-MAJOR cell grid, residual / weight /
+// Jacobian / normal equations of the matched rows, and -- in the last block of a pair to finish --
+// the solve and the pose update.  One launch per ICP iteration (the default for m >= 8192).
+// ---------------------------------------------------------------------------------------------
+// Grid: the same G x G square as the Morton backend, but the targets are sorted by the ROW-MAJOR key
+// y G + x, so a horizontal run of cells [x0, x1] of row y is ONE contiguous range of the sorted copy:
+// start[y G + x0] .. start[y G + x1 + 1].  With an upper bound D on the nearest distance every target
+// that can win or tie lies in the disc of radius D around the query; the disc is covered row by row --
+// lane r of the warp owns cell row ylo + r, computes the half-width of the disc in that row band
+// (fp32, widened by the rounding bound `ferr`) and fetches the two ends of its run: two loads per
+// row, all rows of the disc in parallel, no level search, no sub-cell pass, and the scanned area follows
+// the disc at the resolution of the finest cells instead of a 3 x 3 block of coarser ones.  The warp
+// then walks the non-empty runs with coalesced 16-byte loads; every candidate is compared exactly
+// (fp64 on the caller's coordinates, ties to the lowest original index; for fp32 inputs a conservative
+// fp32 filter sits in front) -- the same comparison as the other two backends, hence the same indices.
+//
+// Block = 8 warps x GRID_ROWS_QW queries, one warp per query at a time.  After the search the indices of the
+// block's queries sit in shared memory and warp 0 evaluates their residual rows one per lane (what
+// icp_step_kernel does per point), reduces the NV sums over the warp with a fixed butterfly, and
+// parks them in the block's slot of a per-pair partial table.  A per-pair arrival counter elects the
+// last block of the pair: it adds the slots in slot order (deterministic whatever the scheduling),
+// solves, updates the pose, writes the histories and the convergence flags, and re-arms the counter.
+constexpr int GRID_ROWS_WARPS = 8;
+#ifndef MMB_ROWS_QW
+#define MMB_ROWS_QW 4
+#endif
+#ifndef MMB_ROWS_MINBLOCKS
+#define MMB_ROWS_MINBLOCKS 5
+#endif
+constexpr int GRID_ROWS_QW = MMB_ROWS_QW;                       // queries per warp
+constexpr int GRID_ROWS_QB = GRID_ROWS_WARPS * GRID_ROWS_QW;    // queries per block (<= 32: one lane each in the row pass)
+constexpr int GRID_ROWS_NVS = 32;                               // doubles per partial slot (NV <= 31)
+static_assert(GRID_ROWS_QB <= 32, "the row pass maps one query to one lane of warp 0");
+
+__host__ __device__ __forceinline__ int rows_key(int x, int y) { return y * GRID_G + x; }
+
+struct RowsArgs {
+  const void* source; const void* target; const void* weight;
+  IcpWorkspace w; IcpSaved sv;
+  void* deltas; void* weights_hist; void* costs;
+  RowParams rp;
+  int N, n, m, cols, K, it, const_iter, save, has_weight, nblk;
+  int warm;                      // 1: idx_cur holds the previous iteration's correspondences
+  double tol, match_thresh;
+};
+
+__device__ __forceinline__ float sqrt_upper_ff(float v) {
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(v));
+  return r * 1.00000048f;
+}
+
+template <typename T, int ICP, int DIM, bool FUSED>
+__global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_rows_kernel(RowsArgs a) {
+  constexpr int D = Dof<DIM>::D;
+  constexpr int NA = D * (D + 1) / 2;
+  constexpr int NV = NA + D + 4;
+  constexpr int ROWS = ICP == MMB_PT2PT ? 3 : 1;
+  pdl_wait();
+  pdl_trigger();
+  const int b = blockIdx.y, blk = blockIdx.x, it = a.it;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (FUSED && a.w.counters[1] && it >= a.w.counters[1]) return;   // every pair converged in an earlier iteration
+  const int R = a.n * ROWS;
+  const int q_first = blk * GRID_ROWS_QB;
+
+  if (FUSED && a.w.frozen[b]) {
+    // prior weights are zero (ICP.py:246-247): the step is 0 and the histories repeat (ICP.py:215-224)
+    T* wh = static_cast<T*>(a.weights_hist) + ((size_t)b * a.K + it) * R;
+    for (int i = q_first * ROWS + tid; i < min((q_first + GRID_ROWS_QB) * ROWS, R); i += blockDim.x)
+      wh[i] = it > 0 ? wh[i - (ptrdiff_t)R] : (T)0;
+    if (blk == 0) {
+      T* dl = static_cast<T*>(a.deltas) + ((size_t)b * a.K + it) * 6;
+      if (tid < 6) dl[tid] = (T)0;
+      if (tid == 0) {
+        static_cast<T*>(a.costs)[(size_t)b * a.K + it] = from_double<T>(a.w.prev_cost[b]);
+        a.w.n_matched[b] = 0;
+        if (a.save) a.sv.active[(size_t)it * a.N + b] = 0;
+      }
+    }
+    return;
+  }
+
+  __shared__ double sP[12];
+  __shared__ double sG[4];
+  __shared__ int sIdx[GRID_ROWS_QB];
+  __shared__ double sTot[GRID_ROWS_NVS];
+  struct Bases { const T* src; const T* tgt; const int* start; const void* sorted; };
+  __shared__ Bases sB;
+  if (tid < 12) sP[tid] = a.w.pose[(size_t)b * 12 + tid];
+  if (tid < 4) sG[tid] = a.w.geom[(size_t)b * 4 + tid];
+  if (tid == 32) {
+    sB.src = static_cast<const T*>(a.source) + (size_t)b * a.n * 3;
+    sB.tgt = static_cast<const T*>(a.target) + (size_t)b * a.m * a.cols;
+    sB.start = a.w.cell_start + (size_t)b * GRID_STRIDE;
+    sB.sorted = static_cast<const SortedPoint<T>*>(a.w.sorted) + (size_t)b * a.m;
+  }
+  __syncthreads();
+  const T* src = sB.src; const T* tgt = sB.tgt;
+  const int* start = sB.start;
+  const SortedPoint<T>* sorted = static_cast<const SortedPoint<T>*>(sB.sorted);
+
+  // ------------------------------- search: one warp per query ----------------------------------
+  for (int kq = 0; kq < GRID_ROWS_QW; ++kq) {
+    const int slot = warp * GRID_ROWS_QW + kq;
+    const int qi = q_first + slot;
+    if (qi >= a.n) break;                                    // whole warp
+    double qx, qy, qz;
+    transform_query<T, DIM>(src + (size_t)qi * 3, sP, qx, qy, qz);
+    double fx = (qx - sG[0]) * sG[2], fy = (qy - sG[1]) * sG[2];
+    if (!(fx > -1.0e12 && fx < 1.0e12)) fx = fx > 0.0 ? 1.0e12 : -1.0e12;      // also catches NaN
+    if (!(fy > -1.0e12 && fy < 1.0e12)) fy = fy > 0.0 ? 1.0e12 : -1.0e12;
+    const bool inside = fx >= 0.0 && fx < (double)GRID_G && fy >= 0.0 && fy < (double)GRID_G;
+    constexpr double SLACK = 9.5367431640625e-07;            // 2^-20
+    const double abs_slack = 1.0e-9 * (1.0 + fabs(fx) + fabs(fy));
+    // fp32 copies for the cell arithmetic: it only decides WHICH cells are looked at, and every fp32
+    // quantity is widened by `ferr`, a bound on its accumulated rounding error in cells
+    const float fxf = (float)fx, fyf = (float)fy;
+    const float ferr = 1.0e-6f * (300.0f + fabsf(fxf) + fabsf(fyf));
+
+    double D2 = 1.0e308; int I = INT_MAX;                    // per-lane partial minimum
+    constexpr bool FILTER = MMB_GRID_FILTER && sizeof(T) == 4;
+    const float qxf = (float)qx, qyf = (float)qy, qzf = (float)qz;
+    const double q1 = fabs(qx) + fabs(qy) + (DIM == 3 ? fabs(qz) : 0.0);
+    float thr = __int_as_float(0x7f800000);                  // +inf until a bound is known
+    auto set_thr = [&]() {                                   // see nn_grid_kernel: every target with d <= D passes
+      if (!FILTER) return;
+      double t = sqrt_upper(D2) * (1.0 + 4.76837158203125e-07) + 1.1920928955078125e-07 * q1;
+      t = t * t * (1.0 + 4.76837158203125e-07);
+      thr = __double2float_ru(t);
+    };
+    auto scan = [&](int s0, int e0) {
+      const SortedPoint<T>* ptr = sorted + (s0 + lane);
+      for (int left = e0 - s0 - lane; left > 0; left -= 32, ptr += 32) {
+        if (FILTER) {
+          const float4 v = __ldg(reinterpret_cast<const float4*>(ptr));
+          const float dxf = v.x - qxf, dyf = v.y - qyf;
+          float f = fmaf(dyf, dyf, dxf * dxf);
+          if (DIM == 3) { const float dzf = v.z - qzf; f = fmaf(dzf, dzf, f); }
+          if (f <= thr) {
+            const double dx = (double)v.x - qx, dy = (double)v.y - qy;
+            double e2 = fma(dy, dy, __dmul_rn(dx, dx));
+            if (DIM == 3) { const double dz = (double)v.z - qz; e2 = fma(dz, dz, e2); }
+            const int j = __float_as_int(v.w);
+            if (e2 < D2 || (e2 == D2 && j < I)) { D2 = e2; I = j; set_thr(); }
+          }
+        } else {
+          double tx, ty, tz; int j;
+          load_sorted(ptr, tx, ty, tz, j);
+          const double dx = tx - qx, dy = ty - qy;
+          double e2 = fma(dy, dy, __dmul_rn(dx, dx));
+          if (DIM == 3) { const double dz = tz - qz; e2 = fma(dz, dz, e2); }
+          if (e2 < D2 || (e2 == D2 && j < I)) { D2 = e2; I = j; }
+        }
+      }
+    };
+    // walk the non-empty runs (s0, e0) the lanes hold
+    auto walk = [&](int s0, int e0) {
+      unsigned mask = __ballot_sync(0xffffffffu, e0 > s0);
+      while (mask) {
+        const int c = __ffs(mask) - 1; mask &= mask - 1;
+        scan(__shfl_sync(0xffffffffu, s0, c), __shfl_sync(0xffffffffu, e0, c));
+      }
+    };
+    // every cell that can hold a target within Dc cells of the query (Dcf: fp32, rounded up and widened)
+    auto scan_disc = [&](float Dcf) {
+      const int ylo = clamp_cell_f(fyf - Dcf), yhi = clamp_cell_f(fyf + Dcf);
+      const float D2c = __fmul_ru(Dcf, Dcf);
+      for (int y0 = ylo; y0 <= yhi; y0 += 32) {
+        const int y = y0 + lane;
+        int s0 = 0, e0 = 0;
+        if (y <= yhi) {
+          const float yf = (float)y;
+          // distance from the query to the row band [y, y+1], shortened by ferr (never too long)
+          const float dy = fmaxf(fmaxf(yf - fyf, fyf - (yf + 1.0f)) - ferr, 0.0f);
+          const float h2 = fmaf(-dy, dy, D2c);
+          if (h2 >= 0.0f) {                                  // else no point of this row is within Dc
+            const float hw = sqrt_upper_ff(h2) + ferr;
+            if (fxf + hw >= 0.0f && fxf - hw < (float)GRID_G) {
+              const int* rowp = start + y * GRID_G;
+              s0 = __ldg(rowp + clamp_cell_f(fxf - hw));
+              e0 = __ldg(rowp + clamp_cell_f(fxf + hw) + 1);
+            }
+          }
+        }
+        walk(s0, e0);
+      }
+    };
+    // cold start: the square of cells [x0, x1] x [y0, y1] (already clamped to the grid)
+    auto scan_square = [&](int x0, int x1, int ylo, int yhi) {
+      for (int y0 = ylo; y0 <= yhi; y0 += 32) {
+        const int y = y0 + lane;
+        int s0 = 0, e0 = 0;
+        if (y <= yhi) { const int* rowp = start + y * GRID_G; s0 = __ldg(rowp + x0); e0 = __ldg(rowp + x1 + 1); }
+        walk(s0, e0);
+      }
+    };
+    auto scan_outside = [&]() { scan(__ldg(start + GRID_OUTSIDE), __ldg(start + GRID_OUTSIDE + 1)); };
+    auto reduce = [&]() {                                    // lexicographic (D2, I) minimum, left in every lane
+      const unsigned long long bits = (unsigned long long)__double_as_longlong(D2);
+      const unsigned hi = (unsigned)(bits >> 32), lo = (unsigned)bits;
+      const unsigned mhi = __reduce_min_sync(0xffffffffu, hi);
+      const unsigned mlo = __reduce_min_sync(0xffffffffu, hi == mhi ? lo : 0xffffffffu);
+      const bool mine = hi == mhi && lo == mlo;
+      I = __reduce_min_sync(0xffffffffu, mine ? I : INT_MAX);
+      D2 = __longlong_as_double((long long)(((unsigned long long)mhi << 32) | mlo));
+      set_thr();
+    };
+
+    bool done = false;
+    if (a.warm) {
+      const int j0 = a.w.idx_cur[(size_t)b * a.n + qi];
+      if (j0 >= 0 && j0 < a.m) {
+        const double d0 = exact_dist2<T, DIM>(tgt + (size_t)j0 * a.cols, qx, qy, qz);
+        if (d0 < 1.0e300) { D2 = d0; I = j0; set_thr(); }
+      }
+    }
+    if (!(D2 < 1.0e300)) {
+      // no bound yet: squares of 3, 5, 9, 17, ... cells around the query's cell until one holds a target
+      D2 = 1.0e308; I = INT_MAX;
+      const int cx = clamp_cell(fx), cy = clamp_cell(fy);
+      int rad = 1;
+      for (;;) {
+        const int x0 = max(cx - rad, 0), x1 = min(cx + rad, GRID_G - 1), y0 = max(cy - rad, 0), y1 = min(cy + rad, GRID_G - 1);
+        scan_square(x0, x1, y0, y1);
+        reduce();
+        if (D2 < 1.0e300) {
+          const double dc = sqrt_upper(D2) * sG[2] * (1.0 + SLACK) + abs_slack;   // cells, inflated
+          const double gap = fmin(fmin(fx, (double)GRID_G - fx), fmin(fy, (double)GRID_G - fy));   // to the grid border
+          // the square holds every cell within `rad` cells of the query: nothing outside it can win or tie
+          done = inside && dc < (double)rad && dc < gap;
+          break;
+        }
+        if (x0 == 0 && y0 == 0 && x1 == GRID_G - 1 && y1 == GRID_G - 1) break;      // the whole grid has been scanned
+        rad *= 2;
+      }
+      if (!(D2 < 1.0e300)) { scan_outside(); reduce(); done = true; }
+    }
+    if (!done) {
+      const double Dc = sqrt_upper(D2) * sG[2] * (1.0 + SLACK) + abs_slack;        // cells, inflated
+      const float Dcf = __double2float_ru(Dc) + ferr;                              // fp32, widened
+      scan_disc(Dcf);
+      if (!(fx - Dc >= 0.0 && fx + Dc < (double)GRID_G && fy - Dc >= 0.0 && fy + Dc < (double)GRID_G)) scan_outside();
+      reduce();
+    }
+    if (lane == 0) {
+      if (FUSED) sIdx[slot] = I;
+      else { const size_t o = (size_t)b * a.n + qi; a.w.pd2[o] = D2; a.w.pidx[o] = I; }
+    }
+  }
+  if (!FUSED) return;
+  __syncthreads();
+  if (warp != 0) return;
+
+  // ------------------------- residual rows of the block's queries: one per lane -----------------
+  const int i = q_first + lane;
+  const bool valid = lane < GRID_ROWS_QB && i < a.n;
+  T* wh = static_cast<T*>(a.weights_hist) + ((size_t)b * a.K + it) * R;
+  double acc[NV];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) acc[k] = 0.0;
+  if (valid) {
+    const size_t o = (size_t)b * a.n + i;
+    int j = sIdx[lane];
+    if (j == INT_MAX) j = 0;
+    a.w.idx_cur[o] = j;
+    if (a.save) a.sv.idx_hist[(size_t)it * a.N * a.n + o] = j;
+    const double px = (double)src[i * 3 + 0], py = (double)src[i * 3 + 1];
+    const double pz = DIM == 3 ? (double)src[i * 3 + 2] : 0.0;
+    double ax, ay, az;
+    rotate_point(sP, px, py, pz, ax, ay, az);
+    const double yx = __dadd_rn(ax, sP[9]), yy = __dadd_rn(ay, sP[10]), yz = __dadd_rn(az, sP[11]);
+    const T* row = tgt + (size_t)j * a.cols;
+    const double dx = yx - (double)row[0], dy = yy - (double)row[1];
+    const double dz = yz - (DIM == 3 ? (double)row[2] : 0.0);
+    const double w0 = a.has_weight ? (double)static_cast<const T*>(a.weight)[o] : 1.0;
+    double j6[ROWS][6], e[ROWS], rho[ROWS];
+    if (ICP == MMB_PT2PL) {
+      const double nx = (double)row[3], ny = (double)row[4], nz = DIM == 3 ? (double)row[5] : 0.0;
+      e[0] = dx * nx + dy * ny + dz * nz;                            // ICP.py:145
+      rho[0] = sqrt(dx * dx + dy * dy + dz * dz);
+      j6[0][0] = ny * az - nz * ay; j6[0][1] = nz * ax - nx * az; j6[0][2] = nx * ay - ny * ax;   // n x a
+      j6[0][3] = -nx; j6[0][4] = -ny; j6[0][5] = -nz;               // ICP.py:165-166
+    } else {
+      const double dd[3] = {dx, dy, dz};
+      const double sk[3][3] = {{0.0, -az, ay}, {az, 0.0, -ax}, {-ay, ax, 0.0}};
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        e[c] = dd[c]; rho[c] = fabs(dd[c]);                          // ICP.py:147, loss.py:45-52
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { j6[c][k] = sk[c][k]; j6[c][3 + k] = (c == k) ? -1.0 : 0.0; }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < ROWS; ++c) {
+      double tw, lw, w;
+      row_weight(a.rp, w0, rho[c], e[c], tw, lw, w);
+      wh[i * ROWS + c] = from_double<T>(w);
+      const double ws = sqrt(w + 1.0e-10) - 1.0e-5;                  // ICP.py:184
+      const double s2 = ws * ws;
+      double jv[D];
+#pragma unroll
+      for (int k = 0; k < D; ++k) jv[k] = j6[c][DIM == 2 ? k + 2 : k];
+      int q = 0;
+#pragma unroll
+      for (int r0 = 0; r0 < D; ++r0) {
+#pragma unroll
+        for (int c0 = r0; c0 < D; ++c0) acc[q++] += s2 * jv[r0] * jv[c0];
+      }
+#pragma unroll
+      for (int k = 0; k < D; ++k) acc[NA + k] += s2 * jv[k] * e[c];
+      acc[NA + D + 0] += s2 * e[c] * e[c];
+      acc[NA + D + 1] += w;
+      acc[NA + D + 2] += (w > a.match_thresh) ? 1.0 : 0.0;
+      acc[NA + D + 3] += (w0 > a.match_thresh) ? 1.0 : 0.0;
+    }
+  }
+  double* slot_out = a.w.partials + ((size_t)b * a.nblk + blk) * GRID_ROWS_NVS;
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const double s = warp_sum(acc[k]);                       // fixed butterfly: the same bits in every lane
+    if (lane == k) __stcg(slot_out + k, s);
+  }
+  __threadfence();                                            // slot and histories before the ticket
+  __syncwarp();
+  int ticket = 0;
+  if (lane == 0) ticket = atomicAdd(a.w.arrive + b, 1);
+  ticket = __shfl_sync(0xffffffffu, ticket, 0);
+  if (ticket != a.nblk - 1) return;
+
+  // ------------------------- last block of the pair: solve and pose update ----------------------
+  __threadfence();
+  if (lane < NV) {
+    const double* col = a.w.partials + (size_t)b * a.nblk * GRID_ROWS_NVS + lane;
+    double s = 0.0;
+    for (int sl = 0; sl < a.nblk; ++sl) s += __ldcg(col + (size_t)sl * GRID_ROWS_NVS);    // slot order: deterministic
+    sTot[lane] = s;
+  }
+  __syncwarp();
+  int allzero = 0;
+  if (lane == 0) {
+    a.w.arrive[b] = 0;                                       // re-armed for the next iteration's launch
+    const double* tot = sTot;
+    T* dl = static_cast<T*>(a.deltas) + ((size_t)b * a.K + it) * 6;
+    T* cs = static_cast<T*>(a.costs) + (size_t)b * a.K + it;
+    double A[D * D], g[D], x[D];
+    int q = 0;
+    for (int r0 = 0; r0 < D; ++r0)
+      for (int c0 = r0; c0 < D; ++c0) { A[r0 * D + c0] = tot[q]; A[c0 * D + r0] = tot[q]; ++q; }
+    for (int k = 0; k < D; ++k) { A[k * D + k] += 1e-12; g[k] = tot[NA + k]; }      // ICP.py:190
+    solve_spd<D>(A, g, x);
+    double d6[6] = {0, 0, 0, 0, 0, 0};
+    for (int k = 0; k < D; ++k) d6[dof_slot<DIM>(k)] = -x[k];                       // ICP.py:191-197
+    if (a.save) {
+      double* Ps = a.sv.pose_hist + ((size_t)it * a.N + b) * 12;
+      for (int k = 0; k < 12; ++k) Ps[k] = sP[k];
+      double* As = a.sv.A_hist + ((size_t)it * a.N + b) * 36;
+      for (int k = 0; k < D * D; ++k) As[k] = A[k];
+      double* Ds = a.sv.delta_hist + ((size_t)it * a.N + b) * 6;
+      for (int k = 0; k < 6; ++k) Ds[k] = d6[k];
+      a.sv.active[(size_t)it * a.N + b] = 1;
+    }
+    // pose update: C <- exp(dphi^)^T C ; r <- r - dr   (ICP.py:200-207)
+    double dC[9], Cn[9];
+    so3_exp(d6, dC);
+    for (int r0 = 0; r0 < 3; ++r0)
+      for (int jx = 0; jx < 3; ++jx) {
+        double s = 0.0;
+        for (int k = 0; k < 3; ++k) s += dC[k * 3 + r0] * sP[k * 3 + jx];
+        Cn[r0 * 3 + jx] = s;
+      }
+    double* P = a.w.pose + (size_t)b * 12;
+    for (int k = 0; k < 9; ++k) P[k] = Cn[k];
+    for (int k = 0; k < 3; ++k) P[9 + k] = sP[9 + k] - d6[3 + k];
+    for (int k = 0; k < 6; ++k) dl[k] = from_double<T>(d6[k]);
+    double cost = tot[NA + D + 0];
+    if (cost == 0.0 && it > 0) cost = a.w.prev_cost[b];                             // ICP.py:220-222
+    a.w.prev_cost[b] = cost;
+    *cs = from_double<T>(cost);
+    const int matched = (int)(tot[NA + D + 2] + 0.5), at_start = (int)(tot[NA + D + 3] + 0.5);
+    a.w.n_matched[b] = matched;
+    a.w.n_start[b] = at_start;
+    double nrm = 0.0;
+    for (int k = 0; k < 6; ++k) nrm += d6[k] * d6[k];
+    nrm = sqrt(nrm);
+    const bool small = sizeof(T) == 4 ? ((float)nrm < (float)a.tol) : (nrm < a.tol);   // in the tensors' dtype
+    if (small) {
+      a.w.conv[b] = 1;
+      if (!a.const_iter) {                                                          // ICP.py:230-247
+        if (a.w.num_iters[b] == 0.0) a.w.num_iters[b] = (double)(it + 1);
+        if (a.w.match_ratio[b] == 0.0) a.w.match_ratio[b] = (double)matched / (double)(at_start > 0 ? at_start : 1);
+        a.w.frozen[b] = 1;
+        const int nf = atomicAdd(&a.w.counters[0], 1) + 1;
+        if (nf == a.N) a.w.counters[1] = it + 1;                                    // later launches are no-ops
+      }
+    }
+    a.w.counters[2] = it + 1;
+    allzero = (tot[NA + D + 1] == 0.0 && it > 0) ? 1 : 0;
+  }
+  allzero = __shfl_sync(0xffffffffu, allzero, 0);
+  if (allzero) {                        // all weights zero: repeat the previous row (ICP.py:215-218)
+    for (int r = lane; r < R; r += 32) wh[r] = wh[r - (ptrdiff_t)R];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // finish: aligned cloud, T, stats
 // ---------------------------------------------------------------------------------------------
 template <typename T, int DIM>
@@ -1604,12 +2051,17 @@ static int build_grid(const void* source, const void* target, int cols, const Ic
   const size_t total = (size_t)pl.N * pl.m;
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * 16) blocks = 148 * 16;
-  grid_count_kernel<T><<<blocks, 256, 0, st>>>(static_cast<const T*>(target), cols, pl.N, pl.m, w.geom, w.keys, w.cell_cursor);
+  grid_count_kernel<T><<<blocks, 256, 0, st>>>(static_cast<const T*>(target), cols, pl.N, pl.m, w.geom, w.keys, w.cell_cursor,
+                                                pl.grid == 2 ? w.ranks : nullptr);
   if ((rc = check_launch())) return rc;
   grid_scan_kernel<<<pl.N, 1024, 0, st>>>(w.cell_cursor, w.cell_start);
   if ((rc = check_launch())) return rc;
-  grid_scatter_kernel<T><<<blocks, 256, 0, st>>>(static_cast<const T*>(target), cols, pl.N, pl.m, w.keys, w.cell_cursor,
-                                                  static_cast<SortedPoint<T>*>(w.sorted));
+  if (pl.grid == 2)
+    grid_scatter_ranked_kernel<T><<<blocks, 256, 0, st>>>(static_cast<const T*>(target), cols, pl.N, pl.m, w.keys, w.ranks,
+                                                           w.cell_start, static_cast<SortedPoint<T>*>(w.sorted));
+  else
+    grid_scatter_kernel<T><<<blocks, 256, 0, st>>>(static_cast<const T*>(target), cols, pl.N, pl.m, w.keys, w.cell_cursor,
+                                                    static_cast<SortedPoint<T>*>(w.sorted));
   return check_launch();
 }
 
@@ -1629,6 +2081,19 @@ static int launch_grid_nn(const NNArgs& a, const IcpPlan& pl, const IcpWorkspace
   attr[0].val.programmaticStreamSerializationAllowed = a.pdl ? 1 : 0;
   cfg.attrs = attr; cfg.numAttrs = 1;
   cudaLaunchKernelEx(&cfg, nn_grid_kernel<T, DIM>, g);
+  return check_launch();
+}
+
+template <typename T, int ICP, int DIM, bool FUSED>
+static int launch_rows(const RowsArgs& ra, const IcpPlan& pl, int pdl, cudaStream_t st) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)pl.nblk, (unsigned)pl.N); cfg.blockDim = dim3(GRID_ROWS_WARPS * 32);
+  cfg.dynamicSmemBytes = 0; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  cudaLaunchKernelEx(&cfg, icp_rows_kernel<T, ICP, DIM, FUSED>, ra);
   return check_launch();
 }
 
@@ -1715,6 +2180,23 @@ static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* s
     na.bound_in = w.bound; na.bound_S = pl.S_sub;
   }
 
+  if (pl.grid == 2) {
+    // row-major cell grid: ONE fused launch per iteration (search + residual rows + solve in the last block of a pair)
+    RowsArgs ra;
+    ra.source = source; ra.target = target; ra.weight = sa.weight;
+    ra.w = w; ra.sv = sv;
+    ra.deltas = deltas; ra.weights_hist = weights_hist; ra.costs = costs;
+    ra.rp = sa.rp;
+    ra.N = pl.N; ra.n = pl.n; ra.m = pl.m; ra.cols = p->target_cols; ra.K = p->max_iterations;
+    ra.const_iter = p->const_iter; ra.save = save; ra.has_weight = sa.has_weight; ra.nblk = pl.nblk;
+    ra.tol = p->tolerance; ra.match_thresh = p->match_ratio_thresh;
+    for (int it = 0; it < p->max_iterations; ++it) {
+      ra.it = it; ra.warm = it > 0 ? 1 : 0;
+      if (prof && it == 0) prof->mark(2);
+      if ((rc = launch_rows<T, ICP, DIM, true>(ra, pl, it > 0 ? 1 : 0, st))) return rc;
+      if (prof) prof->mark(0);
+    }
+  } else
   for (int it = 0; it < p->max_iterations; ++it) {
     na.idx_prev = it > 0 ? w.idx_cur : nullptr;
     na.it = it; na.pdl = it > 0 ? 1 : 0;
@@ -1784,7 +2266,7 @@ static int validate(const mmb_icp_params* p) {
   if (p->icp_type != MMB_PT2PL && p->icp_type != MMB_PT2PT) return MMB_ERR_UNSUPPORTED;
   if (p->dim != 2 && p->dim != 3) return MMB_ERR_UNSUPPORTED;
   if (p->loss_kind < 0 || p->loss_kind > 2) return MMB_ERR_UNSUPPORTED;
-  if (p->nn_backend < MMB_NN_AUTO || p->nn_backend > MMB_NN_GRID) return MMB_ERR_UNSUPPORTED;
+  if (p->nn_backend < MMB_NN_AUTO || p->nn_backend > MMB_NN_ROWS) return MMB_ERR_UNSUPPORTED;
   return MMB_OK;
 }
 
@@ -1817,7 +2299,14 @@ static int run_nn_search(const IcpPlan& pl, int cols, int dim, const void* query
   na.pd2 = w.pd2; na.pidx = w.pidx;
   na.N = pl.N; na.n = pl.n; na.m = pl.m; na.mp = pl.mp; na.cols = cols;
   na.tiles_per_slice = pl.tiles_per_slice; na.S = pl.S; na.it = 0; na.pdl = 0;
-  if (pl.grid) {
+  if (pl.grid == 2) {
+    if ((rc = build_grid<T, DIM>(query, target, cols, pl, w, st))) return rc;
+    RowsArgs ra = {};
+    ra.source = query; ra.target = target; ra.weight = nullptr;
+    ra.w = w;
+    ra.N = pl.N; ra.n = pl.n; ra.m = pl.m; ra.cols = cols; ra.K = 1; ra.it = 0; ra.warm = 0; ra.nblk = pl.nblk;
+    if ((rc = launch_rows<T, MMB_PT2PL, DIM, false>(ra, pl, 0, st))) return rc;
+  } else if (pl.grid) {
     if ((rc = build_grid<T, DIM>(query, target, cols, pl, w, st))) return rc;
     if ((rc = launch_grid_nn<T, DIM>(na, pl, w, st))) return rc;
   } else {
@@ -1860,6 +2349,8 @@ const char* mmb_status_string(int status) {
 }
 
 const char* mmb_last_cuda_error(void) { return g_last_cuda_error; }
+
+long long mmb_launch_count(void) { return g_launch_count.load(std::memory_order_relaxed); }
 
 size_t mmb_icp_workspace_bytes(const mmb_icp_params* p) {
   if (validate(p)) return 0;
@@ -1950,7 +2441,7 @@ int mmb_nn_search(int32_t N, int32_t n, int32_t m, int32_t target_cols, int32_t 
   if (N <= 0 || n <= 0 || m <= 0 || (target_cols != 3 && target_cols != 6)) return MMB_ERR_INVALID_SHAPE;
   if (dtype != MMB_F32 && dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
   if (dim != 2 && dim != 3) return MMB_ERR_UNSUPPORTED;
-  if (nn_backend < MMB_NN_AUTO || nn_backend > MMB_NN_GRID) return MMB_ERR_UNSUPPORTED;
+  if (nn_backend < MMB_NN_AUTO || nn_backend > MMB_NN_ROWS) return MMB_ERR_UNSUPPORTED;
   if (!query || !target || !idx_out || !workspace) return MMB_ERR_NULL_POINTER;
   if (reinterpret_cast<uintptr_t>(workspace) % 256) return MMB_ERR_MISALIGNED;
   const IcpPlan pl = make_plan(N, n, m, MMB_PT2PL, 3, nn_slices, nn_backend, dtype);

@@ -6,13 +6,18 @@
 #include <float.h>
 #include <limits.h>
 
+#include <atomic>
+
 #include "../../include/mm_masking_b200.h"
 
 namespace mmb {
 
 // ---- error plumbing -------------------------------------------------------------------------
 void set_last_cuda_error(cudaError_t e);
+extern std::atomic<long long> g_launch_count;
+// called once after every kernel launch of the library: error check + launch count
 inline int check_launch() {
+  g_launch_count.fetch_add(1, std::memory_order_relaxed);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { set_last_cuda_error(e); return MMB_ERR_CUDA; }
   return MMB_OK;

@@ -51,7 +51,7 @@ def _check(batch, dim, iters, const_iter=True, tol=1e-5, backends=None):
     from mm_masking_b200 import _capi
     ref, g_ref = _oracle(batch, dim, iters, const_iter, tol)
     done = ref["indices"].shape[0]
-    for backend in backends or (_capi.NN_GRID, _capi.NN_BRUTE):
+    for backend in backends or (_capi.NN_ROWS, _capi.NN_GRID, _capi.NN_BRUTE):
         out, g, idx = _ours(batch, dim, iters, const_iter, tol, backend)
         idx = idx[:done].cpu().numpy().astype(np.int64)
         ref_idx = ref["indices"].numpy()
@@ -91,7 +91,7 @@ def test_dense_map_forces_the_sub_cell_split():
     """200 000 targets in 2-D: level >= 2 cells hold far more than GRID_SPLIT targets, so the far (clutter)
     queries go through the 4 x 4 sub-cell culling."""
     from mm_masking_b200 import synth, _capi
-    _check(synth.make_icp_batch(N=2, n=2000, m=200000, seed=2), dim=2, iters=6, backends=(_capi.NN_GRID,))
+    _check(synth.make_icp_batch(N=2, n=2000, m=200000, seed=2), dim=2, iters=6, backends=(_capi.NN_ROWS, _capi.NN_GRID))
 
 
 def test_half_map_forces_the_outside_bucket():
@@ -102,7 +102,7 @@ def test_half_map_forces_the_outside_bucket():
     tgt = batch["target"]
     gone = tgt[:, :, 0] > 10.0
     tgt[gone] = synth.MAP_PAD_VALUE
-    _check(batch, dim=2, iters=6, backends=(_capi.NN_GRID,))
+    _check(batch, dim=2, iters=6, backends=(_capi.NN_ROWS, _capi.NN_GRID))
 
 
 def test_early_exit_and_freezing_at_scale():

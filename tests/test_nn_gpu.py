@@ -43,7 +43,7 @@ def test_exact_ties_take_the_lowest_index(dtype, dim):
     q[:, ::2] += 0.01
     if dim == 2:
         q[:, :, 2] = 0
-    for slices, backend in ((0, 1), (2, 1), (5, 1), (0, 2)):
+    for slices, backend in ((0, 1), (2, 1), (5, 1), (0, 2), (0, 3)):
         idx = nearest_index(q.cuda(), tgt.cuda(), dim=dim, nn_slices=slices, nn_backend=backend).cpu()
         ref = O.nearest_index(q.double(), tgt.double(), "exact")
         assert torch.equal(idx, ref)
@@ -65,7 +65,7 @@ def test_random_clouds_match_oracle(shape, dtype):
         if dim == 2:
             qq[:, :, 2] = 0; tt[:, :, 2] = 0
         ref = O.nearest_index(qq, tt, "exact")
-        for backend in (0, 1, 2):                                       # auto, brute force, cell grid
+        for backend in (0, 1, 2, 3):                                    # auto, brute force, Morton grid, row-major grid
             idx = nearest_index(q.cuda(), tgt.cuda(), dim=dim, nn_backend=backend).cpu()
             assert torch.equal(idx, ref), f"backend {backend}"
 
@@ -79,7 +79,7 @@ def test_clustered_near_ties_fp64_queries():
     centers = torch.rand((N, m // 8, 3), generator=g, dtype=torch.float64) * 150 - 75
     tgt = centers.repeat_interleave(8, dim=1) + 1e-6 * torch.randn((N, m, 3), generator=g, dtype=torch.float64)
     q = centers[:, :n] + 1e-3 * torch.randn((N, n, 3), generator=g, dtype=torch.float64)
-    for backend in (1, 2):
+    for backend in (1, 2, 3):
         idx = nearest_index(q.cuda(), tgt.cuda(), dim=3, nn_backend=backend).cpu()
         assert torch.equal(idx, O.nearest_index(q, tgt, "exact"))
 
@@ -98,7 +98,7 @@ def test_cold_start_bound_pass_keeps_every_tie():
     q = centers[:, :n] + 1e-3 * torch.randn((N, n, 3), generator=g, dtype=torch.float64)
     for dtype in (torch.float64, torch.float32):
         qq, tt = q.to(dtype), tgt.to(dtype)
-        for slices, backend in ((0, 1), (3, 1), (0, 2)):
+        for slices, backend in ((0, 1), (3, 1), (0, 2), (0, 3)):
             idx = nearest_index(qq.cuda(), tt.cuda(), dim=3, nn_slices=slices, nn_backend=backend).cpu()
             assert torch.equal(idx, O.nearest_index(qq.double(), tt.double(), "exact"))
 
@@ -125,5 +125,6 @@ def test_cell_grid_clamped_cells_and_far_queries(dtype):
         if dim == 2:
             qq[:, :, 2] = 0; tt[:, :, 2] = 0
         ref = O.nearest_index(qq, tt, "exact")
-        idx = nearest_index(q.cuda(), tgt.cuda(), dim=dim, nn_backend=2).cpu()
-        assert torch.equal(idx, ref)
+        for backend in (2, 3):
+            idx = nearest_index(q.cuda(), tgt.cuda(), dim=dim, nn_backend=backend).cpu()
+            assert torch.equal(idx, ref), backend
