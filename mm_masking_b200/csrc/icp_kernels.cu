@@ -62,10 +62,7 @@ constexpr double GRID_MARGIN_REL = 0.125;       // ... plus this fraction of its
 constexpr int GRID_OUTSIDE = GRID_CELLS;        // key of the targets that lie outside the grid
 constexpr int GRIDNN_THREADS = 256;
 constexpr int GRID_STRIDE = GRID_CELLS + 8;     // ints per pair in the start / cursor tables (16-byte aligned rows)
-#ifndef MMB_ROWS_QW
-#define MMB_ROWS_QW 4
-#endif
-constexpr int GRID_ROWS_QB_HOST = 8 * MMB_ROWS_QW;   // queries per block of icp_rows_kernel (8 warps x MMB_ROWS_QW)
+constexpr int GRID_ROWS_QB_HOST = 32;           // queries per block of icp_rows_kernel
 
 struct IcpPlan {
   int N, n, m, mp, R;            // mp: m rounded up to NN_TILE; R residual rows
@@ -1254,14 +1251,11 @@ __global__ void __launch_bounds__(STEP_THREADS) icp_step_kernel(StepArgs a) {
 // last block of the pair: it adds the slots in slot order (deterministic whatever the scheduling),
 // solves, updates the pose, writes the histories and the convergence flags, and re-arms the counter.
 constexpr int GRID_ROWS_WARPS = 8;
-#ifndef MMB_ROWS_QW
-#define MMB_ROWS_QW 4
-#endif
 #ifndef MMB_ROWS_MINBLOCKS
 #define MMB_ROWS_MINBLOCKS 5
 #endif
-constexpr int GRID_ROWS_QW = MMB_ROWS_QW;                       // queries per warp
-constexpr int GRID_ROWS_QB = GRID_ROWS_WARPS * GRID_ROWS_QW;    // queries per block (<= 32: one lane each in the row pass)
+constexpr int GRID_ROWS_QB = 32;                                // queries per block: 8 lanes each in phase A/B, one lane each in the row pass
+static_assert(GRID_ROWS_QB == GRID_ROWS_QB_HOST && GRID_ROWS_QB == GRID_ROWS_WARPS * 4, "block layout");
 constexpr int GRID_ROWS_NVS = 32;                               // doubles per partial slot (NV <= 31)
 static_assert(GRID_ROWS_QB <= 32, "the row pass maps one query to one lane of warp 0");
 
@@ -1318,6 +1312,11 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
   __shared__ double sG[4];
   __shared__ int sIdx[GRID_ROWS_QB];
   __shared__ double sTot[GRID_ROWS_NVS];
+  __shared__ double sQ[4][GRID_ROWS_QB];            // position (x, y, z) and squared bound of every query of the block
+  __shared__ int sI[GRID_ROWS_QB];                  // index behind the bound (INT_MAX: none)
+  __shared__ int2 sY[GRID_ROWS_QB];                 // first / last cell row of the disc
+  __shared__ int2 sRuns[GRID_ROWS_QB][32];          // runs (start, end in the sorted copy) of the first 32 rows
+  __shared__ int sNext;                             // next query slot to be taken by a warp
   struct Bases { const T* src; const T* tgt; const int* start; const void* sorted; };
   __shared__ Bases sB;
   if (tid < 12) sP[tid] = a.w.pose[(size_t)b * 12 + tid];
@@ -1327,31 +1326,98 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     sB.tgt = static_cast<const T*>(a.target) + (size_t)b * a.m * a.cols;
     sB.start = a.w.cell_start + (size_t)b * GRID_STRIDE;
     sB.sorted = static_cast<const SortedPoint<T>*>(a.w.sorted) + (size_t)b * a.m;
+    sNext = 0;
   }
   __syncthreads();
   const T* src = sB.src; const T* tgt = sB.tgt;
   const int* start = sB.start;
   const SortedPoint<T>* sorted = static_cast<const SortedPoint<T>*>(sB.sorted);
 
-  // ------------------------------- search: one warp per query ----------------------------------
-  for (int kq = 0; kq < GRID_ROWS_QW; ++kq) {
-    const int slot = warp * GRID_ROWS_QW + kq;
+  // ------------------- phase A/B: bounds and cell runs of the block's 32 queries ------------------
+  // 8 lanes per query (4 queries per warp).  All 8 compute the query's position and its bound D (distance
+  // to the previous iteration's neighbour at the new pose: two dependent loads for 4 queries at once instead
+  // of one query at a time); lane r of the group then fetches the runs of cell rows ylo + r, + 8, + 16, + 24
+  // (up to 8 independent loads in flight per lane) into shared memory.
+  constexpr double SLACK = 9.5367431640625e-07;              // 2^-20
+  // cells of row y that can hold a target within Dcf cells of (fxf, fyf): ends of the run in the sorted copy
+  auto row_run = [&](int y, float fxf, float fyf, float ferr, float D2c) -> int2 {
+    const float yf = (float)y;
+    // distance from the query to the row band [y, y+1], shortened by ferr (never too long)
+    const float dy = fmaxf(fmaxf(yf - fyf, fyf - (yf + 1.0f)) - ferr, 0.0f);
+    const float h2 = fmaf(-dy, dy, D2c);
+    int2 r2 = make_int2(0, 0);
+    if (h2 >= 0.0f) {                                        // else no point of this row is within the bound
+      const float hw = sqrt_upper_ff(h2) + ferr;
+      if (fxf + hw >= 0.0f && fxf - hw < (float)GRID_G) {
+        const int* rowp = start + y * GRID_G;
+        r2.x = __ldg(rowp + clamp_cell_f(fxf - hw));
+        r2.y = __ldg(rowp + clamp_cell_f(fxf + hw) + 1);
+      }
+    }
+    return r2;
+  };
+  {
+    const int g = lane >> 3, r = lane & 7;
+    const int slot = warp * 4 + g, qi = q_first + slot;
+    if (qi < a.n) {
+      double qx, qy, qz;
+      transform_query<T, DIM>(src + (size_t)qi * 3, sP, qx, qy, qz);
+      double D2 = 1.0e308; int I = INT_MAX;
+      if (a.warm) {
+        const int j0 = a.w.idx_cur[(size_t)b * a.n + qi];
+        if (j0 >= 0 && j0 < a.m) {
+          const double d0 = exact_dist2<T, DIM>(tgt + (size_t)j0 * a.cols, qx, qy, qz);
+          if (d0 < 1.0e300) { D2 = d0; I = j0; }
+        }
+      }
+      int2 runs[4] = {make_int2(0, 0), make_int2(0, 0), make_int2(0, 0), make_int2(0, 0)};
+      int ylo = 0, yhi = -1;
+      if (D2 < 1.0e300) {
+        double fx = (qx - sG[0]) * sG[2], fy = (qy - sG[1]) * sG[2];
+        if (!(fx > -1.0e12 && fx < 1.0e12)) fx = fx > 0.0 ? 1.0e12 : -1.0e12;
+        if (!(fy > -1.0e12 && fy < 1.0e12)) fy = fy > 0.0 ? 1.0e12 : -1.0e12;
+        const float fxf = (float)fx, fyf = (float)fy;
+        const float ferr = 1.0e-6f * (300.0f + fabsf(fxf) + fabsf(fyf));
+        const double Dc = sqrt_upper(D2) * sG[2] * (1.0 + SLACK) + 1.0e-9 * (1.0 + fabs(fx) + fabs(fy));
+        const float Dcf = __double2float_ru(Dc) + ferr;
+        const float D2c = __fmul_ru(Dcf, Dcf);
+        ylo = clamp_cell_f(fyf - Dcf); yhi = clamp_cell_f(fyf + Dcf);
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          const int y = ylo + r + 8 * p;
+          if (y <= yhi) runs[p] = row_run(y, fxf, fyf, ferr, D2c);
+        }
+      }
+#pragma unroll
+      for (int p = 0; p < 4; ++p) sRuns[slot][r + 8 * p] = runs[p];
+      if (r == 0) {
+        sQ[0][slot] = qx; sQ[1][slot] = qy; sQ[2][slot] = qz; sQ[3][slot] = D2;
+        sI[slot] = I; sY[slot] = make_int2(ylo, yhi);
+      }
+    }
+  }
+  __syncthreads();
+
+  // ------------- phase C: the warps take the block's queries one at a time, first come first served -------
+  const int nqb = min(GRID_ROWS_QB, a.n - q_first);
+  for (;;) {
+    int slot = 0;
+    if (lane == 0) slot = atomicAdd(&sNext, 1);
+    slot = __shfl_sync(0xffffffffu, slot, 0);
+    if (slot >= nqb) break;
     const int qi = q_first + slot;
-    if (qi >= a.n) break;                                    // whole warp
-    double qx, qy, qz;
-    transform_query<T, DIM>(src + (size_t)qi * 3, sP, qx, qy, qz);
+    const double qx = sQ[0][slot], qy = sQ[1][slot], qz = sQ[2][slot];
+    double D2 = sQ[3][slot]; int I = sI[slot];               // per-lane partial minimum (all lanes start equal)
     double fx = (qx - sG[0]) * sG[2], fy = (qy - sG[1]) * sG[2];
     if (!(fx > -1.0e12 && fx < 1.0e12)) fx = fx > 0.0 ? 1.0e12 : -1.0e12;      // also catches NaN
     if (!(fy > -1.0e12 && fy < 1.0e12)) fy = fy > 0.0 ? 1.0e12 : -1.0e12;
     const bool inside = fx >= 0.0 && fx < (double)GRID_G && fy >= 0.0 && fy < (double)GRID_G;
-    constexpr double SLACK = 9.5367431640625e-07;            // 2^-20
     const double abs_slack = 1.0e-9 * (1.0 + fabs(fx) + fabs(fy));
     // fp32 copies for the cell arithmetic: it only decides WHICH cells are looked at, and every fp32
     // quantity is widened by `ferr`, a bound on its accumulated rounding error in cells
     const float fxf = (float)fx, fyf = (float)fy;
     const float ferr = 1.0e-6f * (300.0f + fabsf(fxf) + fabsf(fyf));
 
-    double D2 = 1.0e308; int I = INT_MAX;                    // per-lane partial minimum
     constexpr bool FILTER = MMB_GRID_FILTER && sizeof(T) == 4;
     const float qxf = (float)qx, qyf = (float)qy, qzf = (float)qz;
     const double q1 = fabs(qx) + fabs(qy) + (DIM == 3 ? fabs(qz) : 0.0);
@@ -1362,21 +1428,26 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
       t = t * t * (1.0 + 4.76837158203125e-07);
       thr = __double2float_ru(t);
     };
+    // exact comparison of one candidate of the sorted copy (fp32 inputs), ties to the lowest original index
+    auto exact_f = [&](const float4& v) {
+      const double dx = (double)v.x - qx, dy = (double)v.y - qy;
+      double e2 = fma(dy, dy, __dmul_rn(dx, dx));
+      if (DIM == 3) { const double dz = (double)v.z - qz; e2 = fma(dz, dz, e2); }
+      const int j = __float_as_int(v.w);
+      if (e2 < D2 || (e2 == D2 && j < I)) { D2 = e2; I = j; set_thr(); }
+    };
+    auto filt = [&](const float4& v) -> float {
+      const float dxf = v.x - qxf, dyf = v.y - qyf;
+      float f = fmaf(dyf, dyf, dxf * dxf);
+      if (DIM == 3) { const float dzf = v.z - qzf; f = fmaf(dzf, dzf, f); }
+      return f;
+    };
     auto scan = [&](int s0, int e0) {
       const SortedPoint<T>* ptr = sorted + (s0 + lane);
       for (int left = e0 - s0 - lane; left > 0; left -= 32, ptr += 32) {
         if (FILTER) {
           const float4 v = __ldg(reinterpret_cast<const float4*>(ptr));
-          const float dxf = v.x - qxf, dyf = v.y - qyf;
-          float f = fmaf(dyf, dyf, dxf * dxf);
-          if (DIM == 3) { const float dzf = v.z - qzf; f = fmaf(dzf, dzf, f); }
-          if (f <= thr) {
-            const double dx = (double)v.x - qx, dy = (double)v.y - qy;
-            double e2 = fma(dy, dy, __dmul_rn(dx, dx));
-            if (DIM == 3) { const double dz = (double)v.z - qz; e2 = fma(dz, dz, e2); }
-            const int j = __float_as_int(v.w);
-            if (e2 < D2 || (e2 == D2 && j < I)) { D2 = e2; I = j; set_thr(); }
-          }
+          if (filt(v) <= thr) exact_f(v);
         } else {
           double tx, ty, tz; int j;
           load_sorted(ptr, tx, ty, tz, j);
@@ -1387,39 +1458,59 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
         }
       }
     };
-    // walk the non-empty runs (s0, e0) the lanes hold
+    // walk the non-empty runs (s0, e0) the lanes hold.  fp32 inputs: four runs at a time -- their first 32
+    // candidates are fetched together (four independent 16-byte loads in flight per lane) and filtered with
+    // one branch; what a run holds beyond 32 candidates is walked afterwards.
     auto walk = [&](int s0, int e0) {
       unsigned mask = __ballot_sync(0xffffffffu, e0 > s0);
-      while (mask) {
-        const int c = __ffs(mask) - 1; mask &= mask - 1;
-        scan(__shfl_sync(0xffffffffu, s0, c), __shfl_sync(0xffffffffu, e0, c));
+      if (!FILTER) {
+        while (mask) {
+          const int c = __ffs(mask) - 1; mask &= mask - 1;
+          scan(__shfl_sync(0xffffffffu, s0, c), __shfl_sync(0xffffffffu, e0, c));
+        }
+        return;
       }
-    };
-    // every cell that can hold a target within Dc cells of the query (Dcf: fp32, rounded up and widened)
-    auto scan_disc = [&](float Dcf) {
-      const int ylo = clamp_cell_f(fyf - Dcf), yhi = clamp_cell_f(fyf + Dcf);
-      const float D2c = __fmul_ru(Dcf, Dcf);
-      for (int y0 = ylo; y0 <= yhi; y0 += 32) {
-        const int y = y0 + lane;
-        int s0 = 0, e0 = 0;
-        if (y <= yhi) {
-          const float yf = (float)y;
-          // distance from the query to the row band [y, y+1], shortened by ferr (never too long)
-          const float dy = fmaxf(fmaxf(yf - fyf, fyf - (yf + 1.0f)) - ferr, 0.0f);
-          const float h2 = fmaf(-dy, dy, D2c);
-          if (h2 >= 0.0f) {                                  // else no point of this row is within Dc
-            const float hw = sqrt_upper_ff(h2) + ferr;
-            if (fxf + hw >= 0.0f && fxf - hw < (float)GRID_G) {
-              const int* rowp = start + y * GRID_G;
-              s0 = __ldg(rowp + clamp_cell_f(fxf - hw));
-              e0 = __ldg(rowp + clamp_cell_f(fxf + hw) + 1);
-            }
+      const float qnan = __int_as_float(0x7fc00000);
+      while (mask) {
+        int sa[4], ea[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          sa[k] = 0; ea[k] = 0;
+          if (mask) {                                        // warp-uniform
+            const int c = __ffs(mask) - 1; mask &= mask - 1;
+            sa[k] = __shfl_sync(0xffffffffu, s0, c); ea[k] = __shfl_sync(0xffffffffu, e0, c);
           }
         }
-        walk(s0, e0);
+        float4 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          v[k] = make_float4(qnan, 0.f, 0.f, 0.f);           // NaN never passes the filter
+          if (sa[k] + lane < ea[k]) v[k] = __ldg(reinterpret_cast<const float4*>(sorted + (sa[k] + lane)));
+        }
+        float f[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) f[k] = filt(v[k]);
+        if (fminf(fminf(f[0], f[1]), fminf(f[2], f[3])) <= thr) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (f[k] <= thr) exact_f(v[k]);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (ea[k] - sa[k] > 32) scan(sa[k] + 32, ea[k]);   // warp-uniform
       }
     };
-    // cold start: the square of cells [x0, x1] x [y0, y1] (already clamped to the grid)
+    // rows yfrom .. yhi of the disc of radius Dcf (cells, fp32, rounded up and widened) around the query
+    auto scan_disc = [&](int yfrom, int yhi, float Dcf) {
+      const float D2c = __fmul_ru(Dcf, Dcf);
+      for (int y0 = yfrom; y0 <= yhi; y0 += 32) {
+        const int y = y0 + lane;
+        int2 r2 = make_int2(0, 0);
+        if (y <= yhi) r2 = row_run(y, fxf, fyf, ferr, D2c);
+        walk(r2.x, r2.y);
+      }
+    };
+    // cold start: the square of cells [x0, x1] x [ylo, yhi] (already clamped to the grid)
     auto scan_square = [&](int x0, int x1, int ylo, int yhi) {
       for (int y0 = ylo; y0 <= yhi; y0 += 32) {
         const int y = y0 + lane;
@@ -1440,16 +1531,20 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
       set_thr();
     };
 
-    bool done = false;
-    if (a.warm) {
-      const int j0 = a.w.idx_cur[(size_t)b * a.n + qi];
-      if (j0 >= 0 && j0 < a.m) {
-        const double d0 = exact_dist2<T, DIM>(tgt + (size_t)j0 * a.cols, qx, qy, qz);
-        if (d0 < 1.0e300) { D2 = d0; I = j0; set_thr(); }
-      }
-    }
-    if (!(D2 < 1.0e300)) {
+    if (D2 < 1.0e300) {
+      // warm start: the first 32 rows of the disc were fetched in phase B
+      set_thr();
+      const int2 run = sRuns[slot][lane];
+      const int2 yy = sY[slot];
+      walk(run.x, run.y);
+      // the bound the rows were chosen with (warp-uniform; the lanes' own minima have moved on)
+      const double Dc = sqrt_upper(sQ[3][slot]) * sG[2] * (1.0 + SLACK) + abs_slack;
+      if (yy.y - yy.x >= 32) scan_disc(yy.x + 32, yy.y, __double2float_ru(Dc) + ferr);
+      if (!(fx - Dc >= 0.0 && fx + Dc < (double)GRID_G && fy - Dc >= 0.0 && fy + Dc < (double)GRID_G)) scan_outside();
+      reduce();
+    } else {
       // no bound yet: squares of 3, 5, 9, 17, ... cells around the query's cell until one holds a target
+      bool done = false;
       D2 = 1.0e308; I = INT_MAX;
       const int cx = clamp_cell(fx), cy = clamp_cell(fy);
       int rad = 1;
@@ -1468,13 +1563,13 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
         rad *= 2;
       }
       if (!(D2 < 1.0e300)) { scan_outside(); reduce(); done = true; }
-    }
-    if (!done) {
-      const double Dc = sqrt_upper(D2) * sG[2] * (1.0 + SLACK) + abs_slack;        // cells, inflated
-      const float Dcf = __double2float_ru(Dc) + ferr;                              // fp32, widened
-      scan_disc(Dcf);
-      if (!(fx - Dc >= 0.0 && fx + Dc < (double)GRID_G && fy - Dc >= 0.0 && fy + Dc < (double)GRID_G)) scan_outside();
-      reduce();
+      if (!done) {
+        const double Dc = sqrt_upper(D2) * sG[2] * (1.0 + SLACK) + abs_slack;        // cells, inflated
+        const float Dcf = __double2float_ru(Dc) + ferr;                              // fp32, widened
+        scan_disc(clamp_cell_f(fyf - Dcf), clamp_cell_f(fyf + Dcf), Dcf);
+        if (!(fx - Dc >= 0.0 && fx + Dc < (double)GRID_G && fy - Dc >= 0.0 && fy + Dc < (double)GRID_G)) scan_outside();
+        reduce();
+      }
     }
     if (lane == 0) {
       if (FUSED) sIdx[slot] = I;
