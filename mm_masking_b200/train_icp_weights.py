@@ -74,7 +74,15 @@ def eval_validation_loss(T_pred, batch_T_gt, gt_eye=True):
 def train_step(model, batch, opt, loss_weights=DEFAULT_LOSS_WEIGHTS, device='cuda', epoch=None, icp_loss_only_iter=0,
                gt_eye=True):
     """One optimiser step on one (already sharded) batch: the body of the loop of `train_policy`
-    (`train_icp_weights.py:31-63`) plus the gradient mean over ranks.  Returns (loss, components)."""
+    (`train_icp_weights.py:31-63`) plus the gradient mean over ranks.  Returns (loss, components).
+
+    Under `torch.distributed` the step equals the single-process step on the whole batch also when the
+    shards are unequal (batch % world != 0): the reference's losses are batch means
+    (`train_icp_weights.py:199-200,226`), so the local loss is weighted by n_local * world / n_global before
+    backward and the plain mean of the gradients over ranks is then the gradient of the global mean.  The
+    UNet gradients are all-reduced bucket by bucket from gradient-ready hooks while backward is still running
+    (`dist.BucketedGradReducer`; every parameter takes part on every rank, missing gradients zero-filled, so
+    the collectives line up), and the returned loss is the mean over the WHOLE batch."""
     batch_scan, batch_map, batch_T = batch['loc_data'], batch['map_data'], batch['transforms']
     batch_T_init = batch_T['T_ml_init'].to(device)
     opt.zero_grad()
@@ -83,10 +91,18 @@ def train_step(model, batch, opt, loss_weights=DEFAULT_LOSS_WEIGHTS, device='cud
     loss, loss_comp = eval_training_loss(T_pred, mask, num_non0, batch_T_gt, batch_scan, batch_map, model,
                                          loss_weights=loss_weights, icp_loss_only_iter=icp_loss_only_iter, gt_eye=gt_eye,
                                          epoch=epoch if epoch is not None else 0)
-    loss.backward()
-    mdist.allreduce_mean_([p.grad for p in model.parameters() if p.grad is not None])
+    n_local = int(batch_T_init.shape[0])
+    reducer = None
+    if mdist.world()[1] > 1:
+        reducer = getattr(model, "_mmb_grad_reducer", None)
+        if reducer is None:
+            reducer = model._mmb_grad_reducer = mdist.BucketedGradReducer(list(model.parameters()))
+        (loss * mdist.shard_loss_scale(n_local, device=loss.device)).backward()
+        reducer.finish()
+    else:
+        loss.backward()
     opt.step()
-    return loss.detach(), loss_comp
+    return mdist.global_mean(loss.detach(), n_local), loss_comp
 
 
 def _staged(iterator, device, prefetch):

@@ -112,3 +112,61 @@ def test_sharded_policy_forward_equals_full_batch():
         full_std = model(*args, mask_only=True).numpy()
     np.testing.assert_allclose(np.concatenate([out[0][0], out[1][0]]), full, atol=1e-6)
     np.testing.assert_allclose(np.concatenate([out[0][1], out[1][1]]), full_std, atol=1e-5)
+
+
+def _toy(seed=0):
+    torch.manual_seed(seed)
+    return torch.nn.Sequential(torch.nn.Linear(6, 16), torch.nn.Tanh(), torch.nn.Linear(16, 16), torch.nn.Tanh(),
+                               torch.nn.Linear(16, 1), torch.nn.Linear(1, 1))
+
+
+def _toy_data():
+    g = torch.Generator().manual_seed(9)
+    return torch.randn((5, 6), generator=g), torch.randn((5, 1), generator=g)
+
+
+def _uneven_worker(rank, ws, port, out):
+    """batch of 5 over 2 ranks (3 + 2): batch-MEAN loss per rank, weighted so that the mean of the gradients
+    over ranks is the gradient of the mean over the whole batch; gradients reduced by the bucketed, hook-driven
+    reducer; rank 1 leaves the last layer out of its graph (no gradient there on that rank)."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(ws))
+    dist.init_process_group("gloo", rank=rank, world_size=ws)
+    try:
+        model = _toy()
+        x, y = _toy_data()
+        s, e = mdist.shard_range(5, ws, rank)
+        red = mdist.BucketedGradReducer(list(model.parameters()), bucket_bytes=64)
+        assert len(red.buckets) >= 3
+        for step in range(2):                                        # twice: the reducer re-arms itself
+            model.zero_grad(set_to_none=True)
+            loss = ((model(x[s:e]) - y[s:e]) ** 2).mean()
+            (loss * mdist.shard_loss_scale(e - s)).backward()
+            red.finish()
+        g = torch.cat([p.grad.reshape(-1) for p in model.parameters()])
+        out[rank] = (g.numpy(), float(mdist.global_mean(loss.detach(), e - s)))
+        # a parameter with no gradient on one rank: the collectives must still line up
+        model.zero_grad(set_to_none=True)
+        body, head = model[:-1], model[-1]
+        pred = body(x[s:e]) if rank == 1 else head(body(x[s:e]))
+        ((pred - y[s:e]) ** 2).mean().backward()
+        red.finish()
+        assert all(p.grad is not None for p in model.parameters())
+        out[10 + rank] = head.weight.grad.numpy().copy()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_unequal_shards_reproduce_the_full_batch_gradient():
+    ws = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_uneven_worker, args=(ws, _free_port(), out), nprocs=ws, join=True)
+    model = _toy()
+    x, y = _toy_data()
+    loss = ((model(x) - y) ** 2).mean()
+    loss.backward()
+    g = torch.cat([p.grad.reshape(-1) for p in model.parameters()]).numpy()
+    for r in range(ws):
+        np.testing.assert_allclose(out[r][0], g, rtol=1e-5, atol=1e-7)
+        assert abs(out[r][1] - float(loss)) < 1e-6
+    np.testing.assert_allclose(out[10], out[11])                     # both ranks hold the same mean
