@@ -282,7 +282,6 @@ def run_ours(args, wl, rank, world, local_rank):
     from mm_masking_b200 import _capi, dist as mdist
     from mm_masking_b200.dICP import ICP
     from mm_masking_b200.prefetch import DevicePrefetcher
-    from mm_masking_b200.dICP.ICP import _IcpFunction  # noqa: F401  (same code path as ICP.icp)
 
     _capi.require_cuda()
     lib = _capi.load_library()

@@ -80,10 +80,10 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
     def sample_bwd():
-        w = ru._SampleWeights.apply(wmask, spts, 0.2384)
+        w = torch.ops.mmb.sample_weights(wmask, spts, 0.2384)
         return w
 
-    w_keep = ru._SampleWeights.apply(wmask, spts, 0.2384)
+    w_keep = torch.ops.mmb.sample_weights(wmask, spts, 0.2384)
     stages = {
         "polar_to_cart_f32": lambda: ru.radar_polar_to_cartesian_diff(fft, az, RES),
         "polar_to_cart_u8": lambda: ru.radar_polar_to_cartesian_diff(raw, az, RES),
@@ -93,7 +93,7 @@ def main():
         "cfar_extract_fused_f32": lambda: ru.cfar_extract_pc(fft, RES, az),
         "extract_pc_from_mask": lambda: ru.extract_pc(mask, RES, az, None, diff=False),
         "kstrong_u8": lambda: ru.kstrong_extract_pc(raw, RES, az),
-        "sample_weights_fwd": lambda: ru._SampleWeights.apply(wmask.detach(), spts, 0.2384),
+        "sample_weights_fwd": lambda: torch.ops.mmb.sample_weights(wmask.detach(), spts, 0.2384),
         "sample_weights_bwd": lambda: torch.autograd.grad(w_keep, wmask, gw, retain_graph=True),
     }
 

@@ -15,6 +15,7 @@
 #include "mmb_common.cuh"
 
 #include <cooperative_groups.h>
+#include <cstdlib>
 #include <vector>
 
 namespace cg = cooperative_groups;
@@ -2211,6 +2212,10 @@ static int launch_grid_nn(const NNArgs& a, const IcpPlan& pl, const IcpWorkspace
 // Queries per block: the blocks of one launch should just fill the resident slots of the GPU (148 SMs x
 // MMB_ROWS_MINBLOCKS blocks), one wave without a tail; a multiple of the 32-query group, at most GRID_ROWS_QBLK_MAX.
 static int rows_queries_per_block(const IcpPlan& pl) {
+  if (const char* e = getenv("MMB_ROWS_QBLK")) {            // tuning override: a multiple of 32 in [32, GRID_ROWS_QBLK_MAX]
+    const int q = atoi(e);
+    if (q >= 32 && q <= GRID_ROWS_QBLK_MAX && q % 32 == 0) return q;
+  }
   const long long slots = 148LL * MMB_ROWS_MINBLOCKS;
   const long long total = (long long)pl.N * pl.n;
   long long q = (total + slots - 1) / slots;

@@ -6,9 +6,9 @@ Mirrors `external/dICP/dICP/ICP.py` of utiasASRL/mm_masking: same constructor, s
 library (`csrc/icp_kernels.cu`) through the C ABI of `include/mm_masking_b200.h`:
 
   icp()  ->  batch_size_handling()  (host: ragged lists -> dense padded tensors, ICP.py:295-497)
-         ->  _IcpFunction.apply     (torch.autograd.Function)
+         ->  torch.ops.mmb.icp_forward   (custom op, mm_masking_b200/ops.py)
                forward : mmb_icp_forward  -- all iterations enqueued without host sync
-               backward: mmb_icp_backward -- adjoint sweep over the saved iterations
+               autograd: torch.ops.mmb.icp_backward -> mmb_icp_backward -- adjoint sweep over the saved iterations
 
 CPU tensors are accepted for drop-in use (the reference's tests pass CPU tensors): they are
 moved to the current CUDA device, and results are returned on the inputs' device.  Without a
@@ -22,115 +22,10 @@ import torch
 import yaml
 
 from .. import _capi
+from .. import ops as _ops  # noqa: F401  (registers torch.ops.mmb.*)
 from .nn import nn
 
 _LOSS_KIND = {"huber": _capi.LOSS_HUBER, "cauchy": _capi.LOSS_CAUCHY}
-
-
-def _zeros_block(device, specs):
-    """zero tensors of the given (shape, dtype) list as 256-byte aligned views of one zero-filled buffer"""
-    spans, total = [], 0
-    for shape, dt in specs:
-        count = 1
-        for d in shape:
-            count *= int(d)
-        nbytes = count * torch.empty((), dtype=dt).element_size()
-        spans.append((total, nbytes))
-        total += (nbytes + 255) // 256 * 256
-    flat = torch.zeros(total, dtype=torch.uint8, device=device)
-    return [flat[o:o + nb].view(dt).view(shape) for (o, nb), (shape, dt) in zip(spans, specs)]
-
-
-class _IcpFunction(torch.autograd.Function):
-    """source (N,n,3), target (N,m,3|6), T_init (N,4,4), weight (N,n) or None -> T, pc (+ histories)."""
-
-    @staticmethod
-    def forward(ctx, source, target, T_init, weight, cfg):
-        lib = _capi.load_library()
-        dev = source.device
-        dtype = source.dtype
-        N, n, _ = source.shape
-        m, cols = target.shape[1], target.shape[2]
-        K = cfg["max_iterations"]
-        rows = 3 * n if cfg["icp_type"] == "pt2pt" else n
-        needs_grad = any(t is not None and t.requires_grad for t in (source, target, T_init, weight))
-
-        p = _capi.IcpParams()
-        p.N, p.n, p.m, p.target_cols = N, n, m, cols
-        p.dtype = _capi.F32 if dtype == torch.float32 else _capi.F64
-        p.icp_type = _capi.PT2PT if cfg["icp_type"] == "pt2pt" else _capi.PT2PL
-        p.dim = cfg["dim"]
-        p.max_iterations = K
-        p.differentiable = int(cfg["differentiable"])
-        p.const_iter = int(cfg["const_iter"])
-        p.use_trim = int(cfg["trim_dist"] is not None and cfg["trim_dist"] >= 0.0)
-        p.trim_dist = float(cfg["trim_dist"]) if p.use_trim else 0.0
-        p.loss_kind = cfg["loss_kind"]
-        p.loss_metric = float(cfg["loss_metric"])
-        p.has_weight = int(weight is not None)
-        p.save_for_backward = int(needs_grad)
-        p.nn_slices = int(cfg.get("nn_slices", 0))
-        p.nn_backend = int(cfg.get("nn_backend", _capi.NN_AUTO))
-        p.tolerance = float(cfg["tolerance"])
-        p.tanh_steepness = float(cfg["tanh_steepness"])
-        p.match_ratio_thresh = float(cfg["match_ratio_thresh"])
-
-        src = source.detach().contiguous()
-        tgt = target.detach().contiguous()
-        T0 = T_init.detach().contiguous()
-        w = None if weight is None else weight.detach().contiguous()
-
-        with torch.cuda.device(dev):
-            ws_bytes = lib.mmb_icp_workspace_bytes(p)
-            sv_bytes = lib.mmb_icp_saved_bytes(p)
-            if ws_bytes == 0:
-                raise _capi.MmbError("mmb_icp_workspace_bytes rejected the parameters")
-            workspace = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-            saved = torch.empty(sv_bytes, dtype=torch.uint8, device=dev) if sv_bytes else None
-            T_out = torch.empty((N, 4, 4), dtype=dtype, device=dev)
-            pc = torch.empty((N, n, 3), dtype=dtype, device=dev)
-            # the zero-initialised outputs (rows of iterations that are not executed stay zero) are carved
-            # from ONE zero-filled block: one fill launch instead of seven
-            deltas, weights, costs, converged, iterations, matched, iters_done = _zeros_block(dev, (
-                ((N, K, 6), dtype), ((N, K, rows), dtype), ((N, K), dtype), ((N,), torch.uint8), ((N,), dtype),
-                ((N,), dtype), ((1,), torch.int32)))
-            rc = lib.mmb_icp_forward(p, _capi.ptr(src), _capi.ptr(tgt), _capi.ptr(T0), _capi.ptr(w),
-                                     _capi.ptr(T_out), _capi.ptr(pc), _capi.ptr(deltas), _capi.ptr(weights),
-                                     _capi.ptr(costs), _capi.ptr(converged), _capi.ptr(iterations),
-                                     _capi.ptr(matched), _capi.ptr(iters_done), _capi.ptr(saved),
-                                     _capi.ptr(workspace), ws_bytes, _capi.stream_ptr())
-            _capi.check(rc, "mmb_icp_forward")
-
-        if cfg.get("record_indices") and saved is not None:
-            # test hook: the correspondences of every executed iteration, (K,N,n) int32 -- the first block of `saved`
-            cfg["indices_out"] = saved[:K * N * n * 4].view(torch.int32).view(K, N, n)
-        ctx.params = p
-        ctx.has_weight = weight is not None
-        ctx.save_for_backward(src, tgt, w if w is not None else src.new_empty(0), saved if saved is not None else src.new_empty(0))
-        ctx.mark_non_differentiable(deltas, weights, costs, converged, iterations, matched, iters_done)
-        return T_out, pc, deltas, weights, costs, converged, iterations, matched, iters_done
-
-    @staticmethod
-    def backward(ctx, g_T, g_pc, *unused):
-        lib = _capi.load_library()
-        src, tgt, w, saved = ctx.saved_tensors
-        p = ctx.params
-        dev = src.device
-        need_src, need_tgt, need_T, need_w = ctx.needs_input_grad[:4]
-        need_w = need_w and ctx.has_weight
-        g_T = None if g_T is None else g_T.contiguous()
-        g_pc = None if g_pc is None else g_pc.contiguous()
-        with torch.cuda.device(dev):
-            g_src = torch.empty_like(src) if need_src else None
-            g_tgt = torch.zeros_like(tgt) if need_tgt else None
-            g_T0 = torch.empty((p.N, 4, 4), dtype=src.dtype, device=dev) if need_T else None
-            g_w = torch.empty((p.N, p.n), dtype=src.dtype, device=dev) if need_w else None
-            rc = lib.mmb_icp_backward(p, _capi.ptr(src), _capi.ptr(tgt), _capi.ptr(w if ctx.has_weight else None),
-                                      _capi.ptr(saved), _capi.ptr(g_T), _capi.ptr(g_pc), _capi.ptr(g_src),
-                                      _capi.ptr(g_tgt), _capi.ptr(g_T0), _capi.ptr(g_w), _capi.ptr(None), 0,
-                                      _capi.stream_ptr())
-            _capi.check(rc, "mmb_icp_backward")
-        return g_src, g_tgt, g_T0, g_w, None
 
 
 class ICP:
@@ -193,16 +88,26 @@ class ICP:
         weight_arg = None
         if has_weight:
             weight_arg = w_init.to(device=dev, dtype=source.dtype)
-        cfg = dict(icp_type=self.icp_type, max_iterations=int(self.max_iterations), tolerance=self.tolerance,
-                   differentiable=bool(self.diff), const_iter=bool(self.const_iter), trim_dist=trim_dist,
-                   loss_kind=loss_kind, loss_metric=loss_metric, dim=int(dim),
-                   tanh_steepness=self.config['dICP']['parameters']['tanh_steepness'],
-                   match_ratio_thresh=self.match_ratio_thresh, nn_slices=self.nn_slices,
-                   nn_backend=self.nn_backend, record_indices=self.record_indices)
-        T, pc, deltas, weights, costs, converged, iterations, matched, iters_done = _IcpFunction.apply(
-            source.to(dev), target.to(dev), T_init.to(dev), weight_arg, cfg)
+        src_d, tgt_d, T0_d = source.to(dev), target.to(dev), T_init.to(dev)
+        needs_grad = torch.is_grad_enabled() and any(
+            t is not None and t.requires_grad for t in (src_d, tgt_d, T0_d, weight_arg))
+        use_trim = trim_dist is not None and trim_dist >= 0.0
+        K = int(self.max_iterations)
+        icp_code = _capi.PT2PT if self.icp_type == 'pt2pt' else _capi.PT2PL
+        T, pc, block, saved = torch.ops.mmb.icp_forward(
+            src_d, tgt_d, T0_d, weight_arg,
+            icp_code, int(dim), K, float(self.tolerance),
+            bool(self.diff), bool(self.const_iter), bool(use_trim), float(trim_dist) if use_trim else 0.0,
+            int(loss_kind), float(loss_metric), float(self.config['dICP']['parameters']['tanh_steepness']),
+            float(self.match_ratio_thresh), int(self.nn_slices), int(self.nn_backend), bool(needs_grad))
+        deltas, weights, costs, converged, iterations, matched, iters_done = _ops._carve(
+            block.detach(), _ops.icp_history_specs(src_d.shape[0], src_d.shape[1], K, icp_code, src_d.dtype))
 
-        self.last_indices = cfg.get("indices_out")
+        # test hook: the correspondences of every iteration, (K,N,n) int32 -- the first block of `saved`
+        self.last_indices = None
+        if self.record_indices and saved.numel():
+            N_, n_ = src_d.shape[0], src_d.shape[1]
+            self.last_indices = saved.detach()[:K * N_ * n_ * 4].view(torch.int32).view(K, N_, n_)
         if self.const_iter:
             it = int(self.max_iterations)    # every pair runs all iterations (dICP_config.yaml:7): no host sync at all
         else:

@@ -11,29 +11,19 @@ supported.
 import torch
 
 from .. import _capi
+from .. import ops as _ops  # noqa: F401  (registers torch.ops.mmb.*)
 
 
 def nearest_index(x: torch.Tensor, y: torch.Tensor, dim: int = 3, nn_slices: int = 0,
                   nn_backend: int = _capi.NN_AUTO) -> torch.Tensor:
     """(N,n) int64 index of the nearest row of y (N,m,3|6) for every row of x (N,n,3)."""
     _capi.require_cuda()
-    lib = _capi.load_library()
     if x.dtype != y.dtype or x.dtype not in (torch.float32, torch.float64):
         raise TypeError("x and y must both be float32 or float64")
     dev = x.device if x.is_cuda else torch.device("cuda", torch.cuda.current_device())
     xq = x.detach().to(dev).contiguous()
     yt = y.detach().to(dev).contiguous()
-    N, n, _ = xq.shape
-    m, cols = yt.shape[1], yt.shape[2]
-    with torch.cuda.device(dev):
-        dt = _capi.F32 if xq.dtype == torch.float32 else _capi.F64
-        ws_bytes = lib.mmb_nn_workspace_bytes(N, n, m, dt, nn_slices, nn_backend)
-        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
-        idx = torch.empty((N, n), dtype=torch.int32, device=dev)
-        rc = lib.mmb_nn_search(N, n, m, cols, dt, dim,
-                               nn_slices, nn_backend, _capi.ptr(xq), _capi.ptr(yt), _capi.ptr(idx), _capi.ptr(ws), ws_bytes,
-                               _capi.stream_ptr())
-        _capi.check(rc, "mmb_nn_search")
+    idx = torch.ops.mmb.nn_search(xq, yt, int(dim), int(nn_slices), int(nn_backend))
     return idx.to(torch.int64).to(x.device)
 
 

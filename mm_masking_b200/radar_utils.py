@@ -24,6 +24,7 @@ import numpy as np
 import torch
 
 from . import _capi
+from . import ops as _ops  # noqa: F401  (registers torch.ops.mmb.*)
 
 _DT = {torch.float32: _capi.F32, torch.float64: _capi.F64}
 
@@ -238,39 +239,6 @@ def kstrong_extract_pc(raw_scans, res, azimuth_angles, kstrong=12, threshold2=0.
 # ---------------------------------------------------------------------------------------------
 # K6: per-point weight sampling
 # ---------------------------------------------------------------------------------------------
-class _SampleWeights(torch.autograd.Function):
-    """mask (N,H,W), pts (N,n,>=2) -> w (N,n); gradient flows to the mask only, as in the reference
-    (`scan_pc` carries no gradient at `icp_weight_policy.py:203`)."""
-
-    @staticmethod
-    def forward(ctx, mask, pts, cart_res):
-        lib = _capi.load_library()
-        N, H, W = mask.shape
-        n, cols = pts.shape[1], pts.shape[2]
-        m = mask.detach().contiguous()
-        with torch.cuda.device(m.device):
-            w = torch.empty((N, n), dtype=m.dtype, device=m.device)
-            _capi.check(lib.mmb_sample_weights_fwd(N, n, cols, H, W, _DT[m.dtype], float(cart_res), _capi.ptr(m),
-                                                   _capi.ptr(pts), _capi.ptr(w), _capi.stream_ptr()),
-                        "mmb_sample_weights_fwd")
-        ctx.save_for_backward(pts)
-        ctx.shape, ctx.cart_res = (N, H, W), float(cart_res)
-        return w
-
-    @staticmethod
-    def backward(ctx, g):
-        lib = _capi.load_library()
-        (pts,) = ctx.saved_tensors
-        N, H, W = ctx.shape
-        g = g.contiguous()
-        with torch.cuda.device(g.device):
-            gm = torch.zeros((N, H, W), dtype=g.dtype, device=g.device)
-            _capi.check(lib.mmb_sample_weights_bwd(N, pts.shape[1], pts.shape[2], H, W, _DT[g.dtype], ctx.cart_res,
-                                                   _capi.ptr(g), _capi.ptr(pts), _capi.ptr(gm), _capi.stream_ptr()),
-                        "mmb_sample_weights_bwd")
-        return gm, None, None
-
-
 def extract_weights(mask, scan_pc):
     """Per-point bilinear sample of the weight mask, same contract as `radar_utils.py:108-140`.
 
@@ -283,7 +251,7 @@ def extract_weights(mask, scan_pc):
     m = mask.to(dev)
     pts = scan_pc.detach().to(device=dev, dtype=m.dtype).contiguous()
     assert m.ndim == 3 and pts.ndim == 3 and m.shape[0] == pts.shape[0]
-    weights = _SampleWeights.apply(m, pts, 0.2384)
+    weights = torch.ops.mmb.sample_weights(m, pts, 0.2384)
     fake = (pts[:, :, 0] == 0.0) & (pts[:, :, 1] == 0.0)
     real = weights[~fake]
     N = weights.shape[0]
@@ -298,38 +266,6 @@ def extract_weights(mask, scan_pc):
 # ---------------------------------------------------------------------------------------------
 # K1: polar -> Cartesian
 # ---------------------------------------------------------------------------------------------
-class _PolarToCart(torch.autograd.Function):
-    """scan (B,A,R) float (or raw uint8 rows) -> (B,width,width); gradient flows to a float scan."""
-
-    @staticmethod
-    def forward(ctx, x, az, rng, ang, meta):
-        lib = _capi.load_library()
-        dt, u8, B, A, R, width, res, cross, wobble = meta
-        with torch.cuda.device(x.device):
-            out = torch.empty((B, width, width), dtype=az.dtype, device=x.device)
-            _capi.check(lib.mmb_polar_to_cart(B, A, R, width, dt, int(u8), _capi.ptr(x), _capi.ptr(az),
-                                              _capi.ptr(rng), _capi.ptr(ang), res, cross, wobble, _capi.ptr(out),
-                                              _capi.stream_ptr()), "mmb_polar_to_cart")
-        ctx.save_for_backward(az, rng, ang)
-        ctx.meta = meta
-        return out
-
-    @staticmethod
-    def backward(ctx, g):
-        lib = _capi.load_library()
-        az, rng, ang = ctx.saved_tensors
-        dt, u8, B, A, R, width, res, cross, wobble = ctx.meta
-        if u8:
-            return None, None, None, None, None
-        g = g.contiguous()
-        with torch.cuda.device(g.device):
-            gs = torch.zeros((B, A, R), dtype=g.dtype, device=g.device)
-            _capi.check(lib.mmb_polar_to_cart_bwd(B, A, R, width, dt, _capi.ptr(g), _capi.ptr(az), _capi.ptr(rng),
-                                                  _capi.ptr(ang), res, cross, wobble, _capi.ptr(gs),
-                                                  _capi.stream_ptr()), "mmb_polar_to_cart_bwd")
-        return gs, None, None, None, None
-
-
 def radar_polar_to_cartesian_diff(fft_data, azimuths, radar_resolution, cart_resolution=0.2384, cart_pixel_width=640,
                                   interpolate_crossover=True, fix_wobble=True):
     """Polar scan batch (B,A,R) -> Cartesian (B,width,width), same contract as `radar_utils.py:258-336`
@@ -347,9 +283,8 @@ def radar_polar_to_cartesian_diff(fft_data, azimuths, radar_resolution, cart_res
     wdt = torch.float32 if dt == _capi.F32 else torch.float64
     az = azimuths.detach().to(device=dev, dtype=wdt).contiguous()
     rng, ang = form_cart_range_angle_grid(cart_pixel_width=cart_pixel_width, dtype=wdt, device=dev)
-    meta = (dt, u8, B, A, R, int(cart_pixel_width), float(radar_resolution), int(bool(interpolate_crossover)),
-            int(bool(fix_wobble)))
-    out = _PolarToCart.apply(x, az, rng, ang, meta)
+    out = torch.ops.mmb.polar_to_cart(x, az, rng.contiguous(), ang.contiguous(), int(cart_pixel_width),
+                                      float(radar_resolution), bool(interpolate_crossover), bool(fix_wobble))
     return out if fft_data.is_cuda else out.to(fft_data.device)
 
 
@@ -364,35 +299,6 @@ def form_polar_range_grid(polar_resolution=0.2384, polar_pixel_shape=(400, 3360)
     return range_coords.unsqueeze(0).expand(polar_pixel_shape[0], -1)
 
 
-class _CartToPolar(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, cart, az, rng, cart_res):
-        lib = _capi.load_library()
-        B, H, W = cart.shape
-        A, R = az.shape[1], rng.shape[0]
-        c = cart.detach().contiguous()
-        with torch.cuda.device(c.device):
-            out = torch.empty((B, A, R), dtype=c.dtype, device=c.device)
-            _capi.check(lib.mmb_cart_to_polar(B, A, R, H, W, _DT[c.dtype], cart_res, _capi.ptr(c), _capi.ptr(az),
-                                              _capi.ptr(rng), _capi.ptr(out), _capi.stream_ptr()), "mmb_cart_to_polar")
-        ctx.save_for_backward(az, rng)
-        ctx.meta = (B, A, R, H, W, cart_res)
-        return out
-
-    @staticmethod
-    def backward(ctx, g):
-        lib = _capi.load_library()
-        az, rng = ctx.saved_tensors
-        B, A, R, H, W, cart_res = ctx.meta
-        g = g.contiguous()
-        with torch.cuda.device(g.device):
-            gc = torch.zeros((B, H, W), dtype=g.dtype, device=g.device)
-            _capi.check(lib.mmb_cart_to_polar_bwd(B, A, R, H, W, _DT[g.dtype], cart_res, _capi.ptr(g), _capi.ptr(az),
-                                                  _capi.ptr(rng), _capi.ptr(gc), _capi.stream_ptr()),
-                        "mmb_cart_to_polar_bwd")
-        return gc, None, None, None
-
-
 def radar_cartesian_to_polar(cart, azimuths, radar_resolution, cart_resolution=0.2384, polar_pixel_shape=(400, 3360)):
     """Cartesian image batch (B,H,W) -> polar (B,A,R), same contract as `radar_utils.py:338-372`,
     differentiable in `cart`.  The reference casts its sampling grid to float64 (`:370`), so it only
@@ -404,7 +310,7 @@ def radar_cartesian_to_polar(cart, azimuths, radar_resolution, cart_resolution=0
     assert c.ndim == 3 and az.ndim == 2 and az.shape[0] == c.shape[0]
     assert az.shape[1] == polar_pixel_shape[0]
     rng = form_polar_range_grid(radar_resolution, polar_pixel_shape, dtype=c.dtype, device=dev)[0].contiguous()
-    out = _CartToPolar.apply(c, az, rng, float(cart_resolution))
+    out = torch.ops.mmb.cart_to_polar(c, az, rng, float(cart_resolution))
     return out if cart.is_cuda else out.to(cart.device)
 
 

@@ -4,7 +4,7 @@
 def test_zero_outputs_are_aligned_views_of_one_block():
     """`ICP.py` carves its zero-initialised outputs from one buffer (one fill launch)"""
     import torch
-    from mm_masking_b200.dICP.ICP import _zeros_block
+    from mm_masking_b200.ops import _zeros_block
     specs = (((3, 10, 6), torch.float64), ((3, 10, 7), torch.float32), ((3,), torch.uint8), ((0, 4), torch.float32),
              ((1,), torch.int32))
     outs = _zeros_block("cpu", specs)
