@@ -63,7 +63,13 @@ constexpr double GRID_MARGIN_REL = 0.125;       // ... plus this fraction of its
 constexpr int GRID_OUTSIDE = GRID_CELLS;        // key of the targets that lie outside the grid
 constexpr int GRIDNN_THREADS = 256;
 constexpr int GRID_STRIDE = GRID_CELLS + 8;     // ints per pair in the start / cursor tables (16-byte aligned rows)
-constexpr int GRID_ROWS_QB_HOST = 32;           // queries per block of icp_rows_kernel
+#ifndef MMB_ROWS_WARPS
+#define MMB_ROWS_WARPS 8
+#endif
+#ifndef MMB_ROWS_INTERLEAVE
+#define MMB_ROWS_INTERLEAVE 0
+#endif
+constexpr int GRID_ROWS_QB_HOST = 4 * MMB_ROWS_WARPS;   // queries per block of icp_rows_kernel (4 per warp)
 
 struct IcpPlan {
   int N, n, m, mp, R;            // mp: m rounded up to NN_TILE; R residual rows
@@ -1251,13 +1257,12 @@ __global__ void __launch_bounds__(STEP_THREADS) icp_step_kernel(StepArgs a) {
 // parks them in the block's slot of a per-pair partial table.  A per-pair arrival counter elects the
 // last block of the pair: it adds the slots in slot order (deterministic whatever the scheduling),
 // solves, updates the pose, writes the histories and the convergence flags, and re-arms the counter.
-constexpr int GRID_ROWS_WARPS = 8;
+constexpr int GRID_ROWS_WARPS = MMB_ROWS_WARPS;
 #ifndef MMB_ROWS_MINBLOCKS
 #define MMB_ROWS_MINBLOCKS 5
 #endif
-constexpr int GRID_ROWS_QB = 32;                                // queries per group: one lane each in the row pass, one partial slot
-constexpr int GRID_ROWS_QBLK_MAX = 256;                         // most queries a block takes (a multiple of 32)
-static_assert(GRID_ROWS_QB == GRID_ROWS_QB_HOST, "group size");
+constexpr int GRID_ROWS_QB = GRID_ROWS_WARPS * 4;               // queries per block: 8 lanes each in phase A/B, one lane each in the row pass
+static_assert(GRID_ROWS_QB == GRID_ROWS_QB_HOST && GRID_ROWS_QB == GRID_ROWS_WARPS * 4, "block layout");
 constexpr int GRID_ROWS_NVS = 32;                               // doubles per partial slot (NV <= 31)
 static_assert(GRID_ROWS_QB <= 32, "the row pass maps one query to one lane of warp 0");
 
@@ -1268,9 +1273,7 @@ struct RowsArgs {
   IcpWorkspace w; IcpSaved sv;
   void* deltas; void* weights_hist; void* costs;
   RowParams rp;
-  int N, n, m, cols, K, it, const_iter, save, has_weight;
-  int nblk;                      // groups of 32 queries (= partial-sum slots) per pair
-  int qblk;                      // queries per block: a multiple of 32, <= GRID_ROWS_QBLK_MAX
+  int N, n, m, cols, K, it, const_iter, save, has_weight, nblk;
   int warm;                      // 1: idx_cur holds the previous iteration's correspondences
   double tol, match_thresh;
 };
@@ -1289,20 +1292,22 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
   constexpr int ROWS = ICP == MMB_PT2PT ? 3 : 1;
   pdl_wait();
   pdl_trigger();
-  const int b = blockIdx.y, bx = blockIdx.x, it = a.it;
+  // consecutive blocks cycle through the pairs, so that at any moment (and in the tail of the launch) the
+  // resident blocks are a mix of cheap (converged) and expensive (far from the map) pairs
+  const int b = MMB_ROWS_INTERLEAVE ? (int)(blockIdx.x % (unsigned)a.N) : (int)blockIdx.y;
+  const int blk = MMB_ROWS_INTERLEAVE ? (int)(blockIdx.x / (unsigned)a.N) : (int)blockIdx.x;
+  const int it = a.it;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  (void)warp;
   if (FUSED && a.w.counters[1] && it >= a.w.counters[1]) return;   // every pair converged in an earlier iteration
   const int R = a.n * ROWS;
-  const int q_first = bx * a.qblk;                          // the block's chunk of the pair's queries
-  const int nq = min(a.qblk, a.n - q_first);
+  const int q_first = blk * GRID_ROWS_QB;
 
   if (FUSED && a.w.frozen[b]) {
     // prior weights are zero (ICP.py:246-247): the step is 0 and the histories repeat (ICP.py:215-224)
     T* wh = static_cast<T*>(a.weights_hist) + ((size_t)b * a.K + it) * R;
-    for (int i = q_first * ROWS + tid; i < (q_first + nq) * ROWS; i += blockDim.x)
+    for (int i = q_first * ROWS + tid; i < min((q_first + GRID_ROWS_QB) * ROWS, R); i += blockDim.x)
       wh[i] = it > 0 ? wh[i - (ptrdiff_t)R] : (T)0;
-    if (bx == 0) {
+    if (blk == 0) {
       T* dl = static_cast<T*>(a.deltas) + ((size_t)b * a.K + it) * 6;
       if (tid < 6) dl[tid] = (T)0;
       if (tid == 0) {
@@ -1316,10 +1321,14 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
 
   __shared__ double sP[12];
   __shared__ double sG[4];
-  __shared__ int sIdx[GRID_ROWS_QBLK_MAX];          // neighbour of every query of the chunk, by slot
-  __shared__ int sDone[GRID_ROWS_QBLK_MAX / 32];    // quads finished per group of 32 queries
+  __shared__ int sIdx[GRID_ROWS_QB];
   __shared__ double sTot[GRID_ROWS_NVS];
-  __shared__ int sNext;                             // next quad (4 queries) to be taken by a warp
+  __shared__ double sQ[4][GRID_ROWS_QB];            // position (x, y, z) and squared bound of every query of the block
+  __shared__ int sI[GRID_ROWS_QB];                  // index behind the bound (INT_MAX: none)
+  __shared__ int2 sY[GRID_ROWS_QB];                 // first / last cell row of the disc
+  __shared__ int2 sRuns[GRID_ROWS_QB][32];          // runs (start, end in the sorted copy) of the first 32 rows
+  __shared__ int sNext;                             // next query slot to be taken by a warp
+  __shared__ T sRow[GRID_ROWS_QB][6];               // matched target row of every query (fetched by the searching warp)
   struct Bases { const T* src; const T* tgt; const int* start; const void* sorted; };
   __shared__ Bases sB;
   if (tid < 12) sP[tid] = a.w.pose[(size_t)b * 12 + tid];
@@ -1331,20 +1340,16 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     sB.sorted = static_cast<const SortedPoint<T>*>(a.w.sorted) + (size_t)b * a.m;
     sNext = 0;
   }
-  if (tid >= 64 && tid < 64 + GRID_ROWS_QBLK_MAX / 32) sDone[tid - 64] = 0;
   __syncthreads();
   const T* src = sB.src; const T* tgt = sB.tgt;
   const int* start = sB.start;
   const SortedPoint<T>* sorted = static_cast<const SortedPoint<T>*>(sB.sorted);
-  const int nquads = (nq + 3) >> 2;
 
-  // The warps of the block take QUADS of four consecutive queries, first come first served; nothing in the
-  // loop synchronises the block.
-  // ------------------- phase A/B: bounds and cell runs of the quad's queries -------------------------
+  // ------------------- phase A/B: bounds and cell runs of the block's 32 queries ------------------
   // 8 lanes per query (4 queries per warp).  All 8 compute the query's position and its bound D (distance
   // to the previous iteration's neighbour at the new pose: two dependent loads for 4 queries at once instead
   // of one query at a time); lane r of the group then fetches the runs of cell rows ylo + r, + 8, + 16, + 24
-  // (up to 8 independent loads in flight per lane) and keeps them in registers.
+  // (up to 8 independent loads in flight per lane) into shared memory.
   constexpr double SLACK = 9.5367431640625e-07;              // 2^-20
   // cells of row y that can hold a target within Dcf cells of (fxf, fyf): ends of the run in the sorted copy
   auto row_run = [&](int y, float fxf, float fyf, float ferr, float D2c) -> int2 {
@@ -1363,19 +1368,10 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     }
     return r2;
   };
-  for (;;) {
-    int quad = 0;
-    if (lane == 0) quad = atomicAdd(&sNext, 1);
-    quad = __shfl_sync(0xffffffffu, quad, 0);
-    if (quad >= nquads) break;
-    // lanes 8g .. 8g+7 hold query g of the quad: position, bound, and the runs of rows ylo + r + 8p in registers
-    double pqx = 0.0, pqy = 0.0, pqz = 0.0, pD2 = 1.0e308;
-    int pI = INT_MAX, pylo = 0, pyhi = -1;
-    int2 runs[4] = {make_int2(0, 0), make_int2(0, 0), make_int2(0, 0), make_int2(0, 0)};
-    {
+  {
     const int g = lane >> 3, r = lane & 7;
-    const int qi = q_first + quad * 4 + g;
-    if (quad * 4 + g < nq) {
+    const int slot = warp * 4 + g, qi = q_first + slot;
+    if (qi < a.n) {
       double qx, qy, qz;
       transform_query<T, DIM>(src + (size_t)qi * 3, sP, qx, qy, qz);
       double D2 = 1.0e308; int I = INT_MAX;
@@ -1386,6 +1382,7 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
           if (d0 < 1.0e300) { D2 = d0; I = j0; }
         }
       }
+      int2 runs[4] = {make_int2(0, 0), make_int2(0, 0), make_int2(0, 0), make_int2(0, 0)};
       int ylo = 0, yhi = -1;
       if (D2 < 1.0e300) {
         double fx = (qx - sG[0]) * sG[2], fy = (qy - sG[1]) * sG[2];
@@ -1403,32 +1400,26 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
           if (y <= yhi) runs[p] = row_run(y, fxf, fyf, ferr, D2c);
         }
       }
-      pqx = qx; pqy = qy; pqz = qz; pD2 = D2; pI = I; pylo = ylo; pyhi = yhi;
+#pragma unroll
+      for (int p = 0; p < 4; ++p) sRuns[slot][r + 8 * p] = runs[p];
+      if (r == 0) {
+        sQ[0][slot] = qx; sQ[1][slot] = qy; sQ[2][slot] = qz; sQ[3][slot] = D2;
+        sI[slot] = I; sY[slot] = make_int2(ylo, yhi);
+      }
     }
-    }
+  }
+  __syncthreads();
 
-  // ------------- phase C: the whole warp searches the quad's queries one after the other -------------------
-  for (int g2 = 0; g2 < 4; ++g2) {
-    const int slot = quad * 4 + g2;
-    if (slot >= nq) break;                                   // whole warp
+  // ------------- phase C: the warps take the block's queries one at a time, first come first served -------
+  const int nqb = min(GRID_ROWS_QB, a.n - q_first);
+  for (;;) {
+    int slot = 0;
+    if (lane == 0) slot = atomicAdd(&sNext, 1);
+    slot = __shfl_sync(0xffffffffu, slot, 0);
+    if (slot >= nqb) break;
     const int qi = q_first + slot;
-    const int lead = g2 * 8;
-    const double qx = __shfl_sync(0xffffffffu, pqx, lead), qy = __shfl_sync(0xffffffffu, pqy, lead);
-    const double qz = DIM == 3 ? __shfl_sync(0xffffffffu, pqz, lead) : 0.0;
-    const double D2_0 = __shfl_sync(0xffffffffu, pD2, lead);
-    double D2 = D2_0; int I = __shfl_sync(0xffffffffu, pI, lead);   // per-lane partial minimum (all lanes start equal)
-    const int ylo_b = __shfl_sync(0xffffffffu, pylo, lead), yhi_b = __shfl_sync(0xffffffffu, pyhi, lead);
-    // row `lane` of the disc: fetched by lane lead + (lane & 7) of phase B as its run number lane >> 3
-    int2 run;
-    {
-      const int sl = lead + (lane & 7), p = lane >> 3;
-      const int x0 = __shfl_sync(0xffffffffu, runs[0].x, sl), x1 = __shfl_sync(0xffffffffu, runs[1].x, sl);
-      const int x2 = __shfl_sync(0xffffffffu, runs[2].x, sl), x3 = __shfl_sync(0xffffffffu, runs[3].x, sl);
-      const int y0 = __shfl_sync(0xffffffffu, runs[0].y, sl), y1 = __shfl_sync(0xffffffffu, runs[1].y, sl);
-      const int y2 = __shfl_sync(0xffffffffu, runs[2].y, sl), y3 = __shfl_sync(0xffffffffu, runs[3].y, sl);
-      run.x = p == 0 ? x0 : (p == 1 ? x1 : (p == 2 ? x2 : x3));
-      run.y = p == 0 ? y0 : (p == 1 ? y1 : (p == 2 ? y2 : y3));
-    }
+    const double qx = sQ[0][slot], qy = sQ[1][slot], qz = sQ[2][slot];
+    double D2 = sQ[3][slot]; int I = sI[slot];               // per-lane partial minimum (all lanes start equal)
     double fx = (qx - sG[0]) * sG[2], fy = (qy - sG[1]) * sG[2];
     if (!(fx > -1.0e12 && fx < 1.0e12)) fx = fx > 0.0 ? 1.0e12 : -1.0e12;      // also catches NaN
     if (!(fy > -1.0e12 && fy < 1.0e12)) fy = fy > 0.0 ? 1.0e12 : -1.0e12;
@@ -1491,17 +1482,21 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
         }
         return;
       }
+      // The runs are cut into chunks of 32 candidates and taken four chunks at a time, whichever runs they
+      // come from: four independent 16-byte loads in flight per lane, one filter branch per 128 candidates.
       const float qnan = __int_as_float(0x7fc00000);
-      while (mask) {
+      int cs = 0, ce = 0;                                    // what is left of the run being cut (warp-uniform)
+      for (;;) {
         int sa[4], ea[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          sa[k] = 0; ea[k] = 0;
-          if (mask) {                                        // warp-uniform
+          if (cs >= ce && mask) {                            // warp-uniform
             const int c = __ffs(mask) - 1; mask &= mask - 1;
-            sa[k] = __shfl_sync(0xffffffffu, s0, c); ea[k] = __shfl_sync(0xffffffffu, e0, c);
+            cs = __shfl_sync(0xffffffffu, s0, c); ce = __shfl_sync(0xffffffffu, e0, c);
           }
+          sa[k] = cs; cs = min(cs + 32, ce); ea[k] = cs;
         }
+        if (sa[0] >= ea[0]) break;                           // nothing left
         float4 v[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
@@ -1516,9 +1511,6 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
           for (int k = 0; k < 4; ++k)
             if (f[k] <= thr) exact_f(v[k]);
         }
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-          if (ea[k] - sa[k] > 32) scan(sa[k] + 32, ea[k]);   // warp-uniform
       }
     };
     // rows yfrom .. yhi of the disc of radius Dcf (cells, fp32, rounded up and widened) around the query
@@ -1540,7 +1532,10 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
         walk(s0, e0);
       }
     };
-    auto scan_outside = [&]() { scan(__ldg(start + GRID_OUTSIDE), __ldg(start + GRID_OUTSIDE + 1)); };
+    // the outside bucket is one run, held by lane 0
+    auto scan_outside = [&]() {
+      walk(lane == 0 ? __ldg(start + GRID_OUTSIDE) : 0, lane == 0 ? __ldg(start + GRID_OUTSIDE + 1) : 0);
+    };
     auto reduce = [&]() {                                    // lexicographic (D2, I) minimum, left in every lane
       const unsigned long long bits = (unsigned long long)__double_as_longlong(D2);
       const unsigned hi = (unsigned)(bits >> 32), lo = (unsigned)bits;
@@ -1555,10 +1550,11 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     if (D2 < 1.0e300) {
       // warm start: the first 32 rows of the disc were fetched in phase B
       set_thr();
-      const int2 yy = make_int2(ylo_b, yhi_b);
+      const int2 run = sRuns[slot][lane];
+      const int2 yy = sY[slot];
       walk(run.x, run.y);
       // the bound the rows were chosen with (warp-uniform; the lanes' own minima have moved on)
-      const double Dc = sqrt_upper(D2_0) * sG[2] * (1.0 + SLACK) + abs_slack;
+      const double Dc = sqrt_upper(sQ[3][slot]) * sG[2] * (1.0 + SLACK) + abs_slack;
       if (yy.y - yy.x >= 32) scan_disc(yy.x + 32, yy.y, __double2float_ru(Dc) + ferr);
       if (!(fx - Dc >= 0.0 && fx + Dc < (double)GRID_G && fy - Dc >= 0.0 && fy + Dc < (double)GRID_G)) scan_outside();
       reduce();
@@ -1591,34 +1587,29 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
         reduce();
       }
     }
-    if (lane == 0) {
-      if (FUSED) sIdx[slot] = I;
-      else { const size_t o = (size_t)b * a.n + qi; a.w.pd2[o] = D2; a.w.pidx[o] = I; }
+    if (FUSED) {
+      // the matched row goes to shared memory now, under the search of the warp's next query, so that the row
+      // pass below starts without a dependent gather
+      if (lane < a.cols) sRow[slot][lane] = tgt[(size_t)(I == INT_MAX ? 0 : I) * a.cols + lane];
+      if (lane == 0) sIdx[slot] = I;
+    } else if (lane == 0) {
+      const size_t o = (size_t)b * a.n + qi; a.w.pd2[o] = D2; a.w.pidx[o] = I;
     }
   }
-    if (!FUSED) continue;
-    // The warp that finishes the last quad of a group of 32 queries evaluates the group's residual rows, one
-    // per lane, while the other warps go on searching.
-    const int grp = quad >> 3;
-    int last_of_group = 0;
-    if (lane == 0) {
-      __threadfence_block();                                 // sIdx of this quad before the count
-      last_of_group = atomicAdd(&sDone[grp], 1) == min(8, nquads - grp * 8) - 1 ? 1 : 0;
-    }
-    last_of_group = __shfl_sync(0xffffffffu, last_of_group, 0);
-    if (!last_of_group) continue;
-    __threadfence_block();
+  if (!FUSED) return;
+  __syncthreads();
+  if (warp != 0) return;
 
-  // ------------------------- residual rows of the group's queries: one per lane ------------------
-  const int i = q_first + grp * 32 + lane;
-  const bool valid = grp * 32 + lane < nq;
+  // ------------------------- residual rows of the block's queries: one per lane -----------------
+  const int i = q_first + lane;
+  const bool valid = lane < GRID_ROWS_QB && i < a.n;
   T* wh = static_cast<T*>(a.weights_hist) + ((size_t)b * a.K + it) * R;
   double acc[NV];
 #pragma unroll
   for (int k = 0; k < NV; ++k) acc[k] = 0.0;
   if (valid) {
     const size_t o = (size_t)b * a.n + i;
-    int j = sIdx[grp * 32 + lane];
+    int j = sIdx[lane];
     if (j == INT_MAX) j = 0;
     a.w.idx_cur[o] = j;
     if (a.save) a.sv.idx_hist[(size_t)it * a.N * a.n + o] = j;
@@ -1627,7 +1618,7 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     double ax, ay, az;
     rotate_point(sP, px, py, pz, ax, ay, az);
     const double yx = __dadd_rn(ax, sP[9]), yy = __dadd_rn(ay, sP[10]), yz = __dadd_rn(az, sP[11]);
-    const T* row = tgt + (size_t)j * a.cols;
+    const T* row = sRow[lane];
     const double dx = yx - (double)row[0], dy = yy - (double)row[1];
     const double dz = yz - (DIM == 3 ? (double)row[2] : 0.0);
     const double w0 = a.has_weight ? (double)static_cast<const T*>(a.weight)[o] : 1.0;
@@ -1672,7 +1663,7 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
       acc[NA + D + 3] += (w0 > a.match_thresh) ? 1.0 : 0.0;
     }
   }
-  double* slot_out = a.w.partials + ((size_t)b * a.nblk + (q_first >> 5) + grp) * GRID_ROWS_NVS;
+  double* slot_out = a.w.partials + ((size_t)b * a.nblk + blk) * GRID_ROWS_NVS;
 #pragma unroll
   for (int k = 0; k < NV; ++k) {
     const double s = warp_sum(acc[k]);                       // fixed butterfly: the same bits in every lane
@@ -1683,11 +1674,22 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
   int ticket = 0;
   if (lane == 0) ticket = atomicAdd(a.w.arrive + b, 1);
   ticket = __shfl_sync(0xffffffffu, ticket, 0);
-  if (ticket != a.nblk - 1) continue;
+  if (ticket != a.nblk - 1) return;
 
   // ------------------------- last block of the pair: solve and pose update ----------------------
   __threadfence();
-  if (lane < NV) {
+  if (NV <= 16) {
+    // columns 0..NV-1 twice: lanes 0..15 add the first half of the slots, lanes 16..31 the second, each in slot
+    // order; the two halves are then added in a fixed order -- deterministic whatever the scheduling
+    const int colk = lane & 15, half = lane >> 4, mid = (a.nblk + 1) >> 1;
+    double s = 0.0;
+    if (colk < NV) {
+      const double* col = a.w.partials + (size_t)b * a.nblk * GRID_ROWS_NVS + colk;
+      for (int sl = half ? mid : 0; sl < (half ? a.nblk : mid); ++sl) s += __ldcg(col + (size_t)sl * GRID_ROWS_NVS);
+    }
+    const double hi = __shfl_down_sync(0xffffffffu, s, 16);
+    if (lane < NV) sTot[lane] = s + hi;
+  } else if (lane < NV) {
     const double* col = a.w.partials + (size_t)b * a.nblk * GRID_ROWS_NVS + lane;
     double s = 0.0;
     for (int sl = 0; sl < a.nblk; ++sl) s += __ldcg(col + (size_t)sl * GRID_ROWS_NVS);    // slot order: deterministic
@@ -1758,7 +1760,6 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
   if (allzero) {                        // all weights zero: repeat the previous row (ICP.py:215-218)
     for (int r = lane; r < R; r += 32) wh[r] = wh[r - (ptrdiff_t)R];
   }
-  }   // quads
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -2209,27 +2210,11 @@ static int launch_grid_nn(const NNArgs& a, const IcpPlan& pl, const IcpWorkspace
   return check_launch();
 }
 
-// Queries per block: the blocks of one launch should just fill the resident slots of the GPU (148 SMs x
-// MMB_ROWS_MINBLOCKS blocks), one wave without a tail; a multiple of the 32-query group, at most GRID_ROWS_QBLK_MAX.
-static int rows_queries_per_block(const IcpPlan& pl) {
-  if (const char* e = getenv("MMB_ROWS_QBLK")) {            // tuning override: a multiple of 32 in [32, GRID_ROWS_QBLK_MAX]
-    const int q = atoi(e);
-    if (q >= 32 && q <= GRID_ROWS_QBLK_MAX && q % 32 == 0) return q;
-  }
-  const long long slots = 148LL * MMB_ROWS_MINBLOCKS;
-  const long long total = (long long)pl.N * pl.n;
-  long long q = (total + slots - 1) / slots;
-  q = (q + 31) / 32 * 32;
-  if (q < 32) q = 32;
-  if (q > GRID_ROWS_QBLK_MAX) q = GRID_ROWS_QBLK_MAX;
-  return (int)q;
-}
-
 template <typename T, int ICP, int DIM, bool FUSED>
-static int launch_rows(RowsArgs ra, const IcpPlan& pl, int pdl, cudaStream_t st) {
-  ra.qblk = rows_queries_per_block(pl);
+static int launch_rows(const RowsArgs& ra, const IcpPlan& pl, int pdl, cudaStream_t st) {
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)((pl.n + ra.qblk - 1) / ra.qblk), (unsigned)pl.N); cfg.blockDim = dim3(GRID_ROWS_WARPS * 32);
+  cfg.gridDim = MMB_ROWS_INTERLEAVE ? dim3((unsigned)pl.nblk * (unsigned)pl.N) : dim3((unsigned)pl.nblk, (unsigned)pl.N);
+  cfg.blockDim = dim3(GRID_ROWS_WARPS * 32);
   cfg.dynamicSmemBytes = 0; cfg.stream = st;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
