@@ -89,6 +89,44 @@ def traffic_lookup(kernel, workload):
     return best.get("dram_bytes_per_launch"), {"traffic_stale": False, "traffic_source": best.get("capture"), "source_sha": sha}
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Pin this rank to the CPU cores local to its GPU BEFORE any pinned host memory is allocated, so that the
+    pinned staging buffers are first-touched on the GPU's NUMA node and 8 ranks do not all upload through one
+    socket (the r01 end-to-end scaling loss).  Reads the PCI topology from sysfs; a no-op when it is not exposed."""
+    try:
+        import torch
+        bus = torch.cuda.get_device_properties(local_rank).pci_bus_id
+        dom = torch.cuda.get_device_properties(local_rank).pci_domain_id
+        dev = torch.cuda.get_device_properties(local_rank).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/local_cpulist"
+        cpus = set()
+        for part in open(path).read().strip().split(","):
+            if "-" in part:
+                a, b = part.split("-"); cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if cpus and cpus != allowed:
+            os.sched_setaffinity(0, cpus)
+            return {"bound": True, "cpus": len(cpus), "numa_node": open(path.replace("local_cpulist", "numa_node")).read().strip()}
+        return {"bound": False, "cpus": len(allowed), "why": "GPU-local CPU list covers the whole allowance"}
+    except Exception as e:                       # containers often hide sysfs topology
+        return {"bound": False, "why": type(e).__name__}
+
+
+def gather_per_rank(value, device):
+    """list of one float per rank (rank order) on every rank"""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        return [float(value)]
+    t = torch.zeros(dist.get_world_size(), dtype=torch.float64, device=device)
+    t[dist.get_rank()] = float(value)
+    dist.all_reduce(t)
+    return [float(x) for x in t.tolist()]
+
+
 def make_batch(wl, seed):
     from mm_masking_b200 import synth
     return synth.make_icp_batch(N=wl["N"], n=wl["n"], m=wl["m"], seed=seed, three_d=wl["three_d"])
@@ -243,6 +281,83 @@ def parity_check(alg, call, wl, batch, dev_tensors, pairs=2):
             "against": "oracle/dicp_oracle.py fp64, nn_mode=kdtree (exhaustive-search semantics), same batch"}
 
 
+def measure_also(args, rank, world, local_rank, dev):
+    """c5 (BASELINE.json configs[4]: 256 pairs GLOBAL, 200 000-point submaps, SE(3), 20 it; strong scaling), c4
+    (configs[3]: training step, global batch 64, NCCL all-reduce of the UNet gradients) and c2 (configs[1]: radar
+    preprocessing, batch 8 per GPU) on the ranks of this run.  Returns the dict on rank 0, None elsewhere."""
+    import torch
+    import torch.distributed as dist
+    from mm_masking_b200 import dist as mdist
+    from mm_masking_b200.dICP import ICP
+    out = {}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- c5, fixed global batch -----------------------------------------------------------------
+    try:
+        wl = WORKLOADS["c5"]
+        G = args.c5_global_pairs
+        s, e = mdist.shard_range(G, world, rank)
+        sub = dict(wl, N=e - s)
+        batch = make_batch(sub, seed=1000 + rank)
+        t = {k: torch.from_numpy(batch[k]).to(dev) for k in ("source", "target", "T_init", "weight")}
+        w = t["weight"].requires_grad_(True)
+        alg = ICP(icp_type="pt2pl", differentiable=True, max_iterations=wl["iters"], tolerance=1e-5)
+        alg.const_iter = True
+        call = dict(trim_dist=5.0, loss_fn={"name": "cauchy", "metric": 1.0}, dim=wl["dim"])
+
+        def step():
+            w.grad = None
+            o = alg.icp(t["source"], t["target"], t["T_init"], weight=w, **call)
+            o["T"].sum().backward()
+
+        for _ in range(2):
+            step()
+        steps = 4
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        barrier()
+        for a, b in ev:
+            a.record(); step(); b.record()
+        barrier()
+        ranks_ms = gather_per_rank(sum(a.elapsed_time(b) for a, b in ev) / steps, dev)
+        par = parity_check(alg, call, wl, batch, (t["source"], t["target"], t["T_init"], w), pairs=1) if rank == 0 else None
+        out["c5"] = {"metric": METRIC, "value": G / (max(ranks_ms) * 1e-3), "unit": UNIT, "n_gpus": world, "scaling": "strong",
+                     "ms_per_step": max(ranks_ms), "per_rank_ms_per_step": ranks_ms, "steps": steps, "warmup": 2,
+                     "config": {"workload": "c5: " + wl["desc"].replace("32 pairs/GPU", f"{G} pairs GLOBAL split over the ranks"),
+                                "global_pairs": G, "pairs_per_gpu": e - s, "n": wl["n"], "m": wl["m"],
+                                "iterations": wl["iters"], "dim": 3, "l2": "working set 2.4 GB per 256 pairs: larger than L2"},
+                     "parity": par}
+        del t, w, batch
+        torch.cuda.empty_cache()
+    except Exception as ex:                                  # an auxiliary measurement must not sink the headline
+        out["c5"] = {"error": f"{type(ex).__name__}: {ex}"}
+    # ---- c4, training step ----------------------------------------------------------------------
+    try:
+        import bench_train
+        targs = bench_train.parse_args(["--gpus", str(world), "--steps", "6", "--warmup", "3"])
+        line = bench_train.run(targs, rank, world, local_rank, own_process_group=False, sample_clocks=False)
+        out["c4"] = line
+        torch.cuda.empty_cache()
+    except Exception as ex:
+        out["c4"] = {"error": f"{type(ex).__name__}: {ex}"}
+    # ---- c2, radar preprocessing (every rank its own batch of 8) -----------------------------------
+    try:
+        import bench_radar
+        rargs = bench_radar.parse_args(["--batch", "8", "--reps", "10", "--no-cpu-baseline"])
+        line = bench_radar.run(rargs, local_rank)
+        ms = gather_per_rank(line["ms_per_step"], dev)
+        ms_e = gather_per_rank(line["e2e"]["ms_per_step"], dev)
+        line.update(value=world * 8 / (max(ms) * 1e-3), n_gpus=world, ms_per_step=max(ms))
+        line["e2e"].update(value=world * 8 / (max(ms_e) * 1e-3), ms_per_step=max(ms_e))
+        out["c2"] = line
+    except Exception as ex:
+        out["c2"] = {"error": f"{type(ex).__name__}: {ex}"}
+    return out if rank == 0 else None
+
+
 def run_reference(args, wl, rank, world):
     import torch
     if rank != 0:
@@ -287,9 +402,10 @@ def run_ours(args, wl, rank, world, local_rank):
     lib = _capi.load_library()
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = bind_to_gpu_numa_node(local_rank)      # before pin_memory()
     if world > 1:
         import datetime
-        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=90))
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))
 
     batch = make_batch(wl, seed=rank)
     N, n, m, K = wl["N"], wl["n"], wl["m"], wl["iters"]
@@ -324,6 +440,8 @@ def run_ours(args, wl, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    per_rank = []
+
     def timed(fn, steps, warmup):
         for _ in range(warmup):
             fn()
@@ -337,8 +455,9 @@ def run_ours(args, wl, rank, world, local_rank):
             b.record()
         barrier()
         t1 = time.time()
-        ms = mdist.max_over_ranks(sum(a.elapsed_time(b) for a, b in ev), device=dev)
-        return ms / steps, t0, t1
+        mine = sum(a.elapsed_time(b) for a, b in ev) / steps
+        per_rank.clear(); per_rank.extend(gather_per_rank(mine, dev))
+        return max(per_rank), t0, t1
 
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
@@ -370,7 +489,8 @@ def run_ours(args, wl, rank, world, local_rank):
             step_e2e(next(pre))
         eb.record()
         barrier()
-        e2e_ms.append(mdist.max_over_ranks(ea.elapsed_time(eb), device=dev) / args.steps)
+        e2e_rank = gather_per_rank(ea.elapsed_time(eb) / args.steps, dev)
+        e2e_ms.append(max(e2e_rank))
     t1 = time.time()
     launches_e2e = lib.mmb_launch_count() - launches1
     h2d_per_step = (pre.bytes_uploaded - up0) // (args.steps * len(e2e_ms))
@@ -389,6 +509,15 @@ def run_ours(args, wl, rank, world, local_rank):
         sampler.stop()
         clocks = sampler.summary(t0, t1)
 
+    per_rank_res = list(per_rank)
+    also = None
+    if args.also:
+        # the other BASELINE.json configs, measured in this process at this N (all ranks take part: c4 holds the
+        # only data-path collective of the package, c5 is a fixed GLOBAL batch split over the ranks)
+        del flush
+        torch.cuda.empty_cache()
+        also = measure_also(args, rank, world, local_rank, dev)
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -541,6 +670,11 @@ def run_ours(args, wl, rank, world, local_rank):
         "roofline_exhaustive_nn": roofline_brute,
         "cpu_baseline": cpu,
         "parity": parity,
+        "per_rank_ms_per_step": {"resident": per_rank_res, "e2e_last_repeat": e2e_rank,
+                                 "min": min(per_rank_res), "median": sorted(per_rank_res)[len(per_rank_res) // 2],
+                                 "max": max(per_rank_res)},
+        "host_binding": numa,
+        "also": also,
         "clocks": clocks,
     }
     print(json.dumps(line), flush=True)
@@ -561,6 +695,10 @@ def main():
     ap.add_argument("--ref-pairs", type=int, default=0,
                     help="pairs per CPU-reference step (bounded sample); 0 = 8 at c3 (BASELINE.md section 3), 1 at c5")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--c5-global-pairs", type=int, default=256)
+    ap.add_argument("--also", type=int, default=1,
+                    help="1: also measure c5 (strong, 256 pairs global), c4 (train steps/s) and c2 (radar scans/s) in this "
+                         "process at this N and report them under \"also\"")
     ap.add_argument("--e2e-repeats", type=int, default=3, help="repeats of the K-step end-to-end loop (median reported)")
     ap.add_argument("--nn-backend", default="auto", choices=sorted(NN_BACKENDS),
                     help="nearest-neighbour backend: exact cell grid (auto for m >= 8192) or brute force; same indices")

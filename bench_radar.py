@@ -45,21 +45,24 @@ def algorithmic_bytes(B, n_points_total, n_k_points):
     }
 
 
-def main():
+def parse_args(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    args = ap.parse_args()
+    return ap.parse_args(argv)
 
+
+def run(args, local_rank=0):
+    """measure the c2 preprocessing chain on cuda:local_rank; returns the JSON line as a dict"""
     import numpy as np
     import torch
     from mm_masking_b200 import _capi, synth, radar_utils as ru
 
     _capi.require_cuda()
     _capi.load_library()
-    dev = torch.device("cuda", 0)
+    dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     B = args.batch
     base = synth.make_radar_scans(B=min(B, 8), seed=0)
@@ -171,7 +174,11 @@ def main():
                      "frac": out_stages[dom]["frac_hbm"], "traffic": None, "peak_source": peak_src},
         "stages": out_stages, "cpu_baseline": cpu,
     }
-    print(json.dumps(line), flush=True)
+    return line
+
+
+def main():
+    print(json.dumps(run(parse_args())), flush=True)
 
 
 if __name__ == "__main__":

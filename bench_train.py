@@ -26,7 +26,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 
-def main():
+def parse_args(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=8)
@@ -34,10 +34,13 @@ def main():
     ap.add_argument("--batch", type=int, default=64, help="GLOBAL batch (pairs per step over all ranks)")
     ap.add_argument("--n", type=int, default=2000)
     ap.add_argument("--m", type=int, default=50000)
-    args = ap.parse_args()
-    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    ap.add_argument("--channels-last", type=int, default=1, help="UNet weights/activations in channels_last (fp32 kept)")
+    return ap.parse_args(argv)
 
+
+def run(args, rank, world, local_rank, own_process_group=True, sample_clocks=True):
+    """measure the c4 training step; returns the JSON line (a dict) on rank 0, None elsewhere.  With
+    own_process_group=False the caller (bench.py --also) has initialised torch.distributed and keeps it."""
     import torch
     import torch.distributed as dist
     from mm_masking_b200 import _capi, synth, dist as mdist
@@ -50,7 +53,7 @@ def main():
     torch.cuda.set_device(local_rank)
     torch.backends.cudnn.benchmark = True            # UNet convolutions (PyTorch/cuDNN, not the product)
     dev = torch.device("cuda", local_rank)
-    if world > 1:
+    if world > 1 and own_process_group:
         import datetime
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=90))
 
@@ -63,6 +66,8 @@ def main():
 
     torch.manual_seed(0)                                    # identical initial weights on every rank
     model = LearnICPWeightPolicy({"device": dev, "max_iter": 10}).to(dev)
+    if args.channels_last:
+        model = model.to(memory_format=torch.channels_last)     # cuDNN NHWC kernels; arithmetic stays fp32
     model.ICP_alg.const_iter = True
     model.train()
     opt = torch.optim.Adam(model.parameters(), lr=1e-4)
@@ -112,7 +117,7 @@ def main():
         total = ev[0][0].elapsed_time(ev[0][1]) if whole else sum(a.elapsed_time(b) for a, b in ev)
         return mdist.max_over_ranks(total, device=dev) / steps, t0, t1
 
-    sampler = ClockSampler(local_rank) if rank == 0 else None
+    sampler = ClockSampler(local_rank) if rank == 0 and sample_clocks else None
     if sampler:
         sampler.start(); time.sleep(0.3)
     ms_res, t0, t1 = timed(step_resident, args.steps, args.warmup)
@@ -147,6 +152,7 @@ def main():
                      "loss_and_backward_all": e4.elapsed_time(e5)}
         opt.zero_grad()
 
+    line = None
     if rank == 0:
         h2d = sum(vv.numel() * vv.element_size() for v in host.values() for vv in v.values())
         n_params = sum(p.numel() for p in model.parameters())
@@ -158,7 +164,7 @@ def main():
             "config": {"workload": "c4: ICP-weight-policy training step (UNet mask -> weight sampling -> dICP 10 it -> "
                                    "pose + occupancy loss -> backward -> Adam), global batch sharded over the ranks",
                        "global_batch": args.batch, "pairs_per_gpu": e - s, "n": args.n, "m": args.m, "iterations": 10,
-                       "image": "640x640", "unet_params": n_params,
+                       "image": "640x640", "unet_params": n_params, "unet_memory_format": "channels_last" if args.channels_last else "contiguous",
                        "l2": "flushed between steps (256 MiB fill, untimed); per-step CUDA events",
                        "parallelism": f"dp{world}: pairs sharded, one flat NCCL all-reduce of the UNet gradients, "
                                       "MIN/MAX all-reduce of the input normalisation"},
@@ -166,9 +172,18 @@ def main():
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
             "breakdown_ms": breakdown, "clocks": clocks,
         }
-        print(json.dumps(line), flush=True)
-    if world > 1:
+    if world > 1 and own_process_group:
         dist.destroy_process_group()
+    return line
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    line = run(args, rank, world, local_rank)
+    if line is not None:
+        print(json.dumps(line), flush=True)
 
 
 if __name__ == "__main__":
