@@ -162,6 +162,13 @@ int mmb_sample_weights_fwd(int32_t N, int32_t n, int32_t pt_cols, int32_t H, int
 int mmb_sample_weights_bwd(int32_t N, int32_t n, int32_t pt_cols, int32_t H, int32_t W,
                            int32_t dtype, double cart_res, const void* grad_w, const void* pts,
                            void* grad_mask, void* stream);
+/* The same adjoint without floating-point atomics: taps sorted by pixel with a stable radix sort,
+ * every run of equal pixels summed in tap order -- bit-identical from run to run.  grad_mask zero-filled by the
+ * caller; workspace: mmb_sample_weights_bwd_det_workspace_bytes, 256-byte aligned. */
+size_t mmb_sample_weights_bwd_det_workspace_bytes(int32_t N, int32_t n, int32_t H, int32_t W, int32_t dtype);
+int mmb_sample_weights_bwd_det(int32_t N, int32_t n, int32_t pt_cols, int32_t H, int32_t W,
+                               int32_t dtype, double cart_res, const void* grad_w, const void* pts,
+                               void* grad_mask, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Polar -> Cartesian resampling.  Replaces radar_utils.py:258-336
  * (`radar_polar_to_cartesian_diff`).  range_tab / angle_tab: the (width*width) pixel-centre tables

@@ -70,6 +70,8 @@ SIGNATURES = {
     "mmb_nn_search": (C.c_int, [C.c_int32] * 8 + [_P] * 4 + [C.c_size_t, _P]),
     "mmb_sample_weights_fwd": (C.c_int, [C.c_int32] * 6 + [C.c_double, _P, _P, _P, _P]),
     "mmb_sample_weights_bwd": (C.c_int, [C.c_int32] * 6 + [C.c_double, _P, _P, _P, _P]),
+    "mmb_sample_weights_bwd_det_workspace_bytes": (C.c_size_t, [C.c_int32] * 5),
+    "mmb_sample_weights_bwd_det": (C.c_int, [C.c_int32] * 6 + [C.c_double, _P, _P, _P, _P, C.c_size_t, _P]),
     "mmb_polar_to_cart": (C.c_int, [C.c_int32] * 6 + [_P] * 4 + [C.c_double, C.c_int32, C.c_int32, _P, _P]),
     "mmb_polar_to_cart_bwd": (C.c_int, [C.c_int32] * 5 + [_P] * 4 + [C.c_double, C.c_int32, C.c_int32, _P, _P]),
     "mmb_cart_to_polar": (C.c_int, [C.c_int32] * 6 + [C.c_double] + [_P] * 5),

@@ -12,6 +12,8 @@
 
 #include <type_traits>
 
+#include <cub/device/device_radix_sort.cuh>
+
 namespace mmb {
 
 // All of these kernels are bound by HBM traffic; grids are sized in whole rows / pixels.
@@ -118,6 +120,90 @@ __global__ void sample_weights_bwd_kernel(const T* __restrict__ grad_w, const T*
   if (inside(t.x0 + 1, t.y0, W, H)) atomicAdd(img + (size_t)t.y0 * W + t.x0 + 1, mul_rn(go, t.ne));
   if (inside(t.x0, t.y0 + 1, W, H)) atomicAdd(img + (size_t)(t.y0 + 1) * W + t.x0, mul_rn(go, t.sw));
   if (inside(t.x0 + 1, t.y0 + 1, W, H)) atomicAdd(img + (size_t)(t.y0 + 1) * W + t.x0 + 1, mul_rn(go, t.se));
+}
+
+// Deterministic form of the adjoint: every tap becomes a (pixel key, contribution) pair, the pairs
+// are sorted by key with a STABLE radix sort (CUB, toolkit library; equal keys keep their tap order), and the
+// first element of every run of equal keys adds the run in that order and stores the sum -- no floating-point
+// atomics, the same bits on every run.  Taps outside the image get the key `total_pixels` and sort to the end.
+template <typename T>
+__global__ void sample_weights_taps_kernel(const T* __restrict__ grad_w, const T* __restrict__ pts, int pt_cols, int N,
+                                           int n, int H, int W, T cart_res, unsigned long long* __restrict__ keys,
+                                           T* __restrict__ vals) {
+  const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= (size_t)N * n) return;
+  const int b = (int)(g / n);
+  T gx, gy;
+  point_grid<T>(pts + g * pt_cols, cart_res, W, gx, gy);
+  const Taps<T> t = bilinear_taps<T>(gx, gy, W, H);
+  const unsigned long long base = (unsigned long long)b * H * W, none = (unsigned long long)N * H * W;
+  const T go = grad_w[g];
+  const int xs[4] = {t.x0, t.x0 + 1, t.x0, t.x0 + 1}, ys[4] = {t.y0, t.y0, t.y0 + 1, t.y0 + 1};
+  const T ws[4] = {t.nw, t.ne, t.sw, t.se};
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const bool in = inside(xs[k], ys[k], W, H);
+    keys[4 * g + k] = in ? base + (unsigned long long)ys[k] * W + xs[k] : none;
+    vals[4 * g + k] = in ? mul_rn(go, ws[k]) : (T)0;
+  }
+}
+
+template <typename T>
+__global__ void sample_weights_runs_kernel(const unsigned long long* __restrict__ keys, const T* __restrict__ vals,
+                                           size_t count, unsigned long long none, T* __restrict__ grad_mask) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  const unsigned long long k = keys[i];
+  if (k >= none || (i > 0 && keys[i - 1] == k)) return;       // not the head of a run
+  T acc = vals[i];
+  for (size_t j = i + 1; j < count && keys[j] == k; ++j) acc = add_rn(acc, vals[j]);
+  grad_mask[k] = acc;
+}
+
+struct SampleBwdWorkspace {
+  unsigned long long *keys_in, *keys_out;
+  void *vals_in, *vals_out, *temp;
+  size_t temp_bytes, bytes;
+};
+
+static int key_bits(unsigned long long none) {
+  int bits = 1;
+  while (bits < 64 && (none >> bits)) ++bits;
+  return bits;
+}
+
+template <typename T>
+static SampleBwdWorkspace carve_sample_bwd(void* base, int N, int n, int H, int W) {
+  Carver c(base);
+  SampleBwdWorkspace w;
+  const size_t count = (size_t)N * n * 4;
+  w.keys_in = c.take<unsigned long long>(count); w.keys_out = c.take<unsigned long long>(count);
+  w.vals_in = c.take<T>(count); w.vals_out = c.take<T>(count);
+  w.temp_bytes = 0;
+  cub::DeviceRadixSort::SortPairs(nullptr, w.temp_bytes, (const unsigned long long*)nullptr, (unsigned long long*)nullptr,
+                                  (const T*)nullptr, (T*)nullptr, count, 0, key_bits((unsigned long long)N * H * W));
+  w.temp = c.take<char>(w.temp_bytes);
+  w.bytes = c.off;
+  return w;
+}
+
+template <typename T>
+static int run_sample_bwd_det(int N, int n, int pt_cols, int H, int W, double cart_res, const void* grad_w, const void* pts,
+                              void* grad_mask, void* workspace, cudaStream_t st) {
+  SampleBwdWorkspace w = carve_sample_bwd<T>(workspace, N, n, H, W);
+  const size_t count = (size_t)N * n * 4;
+  const unsigned long long none = (unsigned long long)N * H * W;
+  sample_weights_taps_kernel<T><<<(int)(((size_t)N * n + 255) / 256), 256, 0, st>>>(
+      static_cast<const T*>(grad_w), static_cast<const T*>(pts), pt_cols, N, n, H, W, (T)cart_res, w.keys_in,
+      static_cast<T*>(w.vals_in));
+  int rc = check_launch();
+  if (rc) return rc;
+  if (cub::DeviceRadixSort::SortPairs(w.temp, w.temp_bytes, w.keys_in, w.keys_out, static_cast<const T*>(w.vals_in),
+                                      static_cast<T*>(w.vals_out), count, 0, key_bits(none), st) != cudaSuccess)
+    return check_launch();
+  sample_weights_runs_kernel<T><<<(int)((count + 255) / 256), 256, 0, st>>>(w.keys_out, static_cast<const T*>(w.vals_out),
+                                                                           count, none, static_cast<T*>(grad_mask));
+  return check_launch();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -789,6 +875,24 @@ int mmb_sample_weights_bwd(int32_t N, int32_t n, int32_t pt_cols, int32_t H, int
                                                               static_cast<const double*>(pts), pt_cols, N, n, H, W,
                                                               cart_res, static_cast<double*>(grad_mask));
   return check_launch();
+}
+
+size_t mmb_sample_weights_bwd_det_workspace_bytes(int32_t N, int32_t n, int32_t H, int32_t W, int32_t dtype) {
+  if (N <= 0 || n <= 0 || H <= 1 || W <= 1) return 0;
+  return dtype == MMB_F64 ? carve_sample_bwd<double>(nullptr, N, n, H, W).bytes : carve_sample_bwd<float>(nullptr, N, n, H, W).bytes;
+}
+
+int mmb_sample_weights_bwd_det(int32_t N, int32_t n, int32_t pt_cols, int32_t H, int32_t W, int32_t dtype, double cart_res,
+                               const void* grad_w, const void* pts, void* grad_mask, void* workspace,
+                               size_t workspace_bytes, void* stream) {
+  if (N <= 0 || n <= 0 || H <= 1 || W <= 1 || pt_cols < 2) return MMB_ERR_INVALID_SHAPE;
+  if (dtype != MMB_F32 && dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  if (!grad_w || !pts || !grad_mask || !workspace) return MMB_ERR_NULL_POINTER;
+  if (reinterpret_cast<uintptr_t>(workspace) % 256) return MMB_ERR_MISALIGNED;
+  if (workspace_bytes < mmb_sample_weights_bwd_det_workspace_bytes(N, n, H, W, dtype)) return MMB_ERR_WORKSPACE_TOO_SMALL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return dtype == MMB_F32 ? run_sample_bwd_det<float>(N, n, pt_cols, H, W, cart_res, grad_w, pts, grad_mask, workspace, st)
+                          : run_sample_bwd_det<double>(N, n, pt_cols, H, W, cart_res, grad_w, pts, grad_mask, workspace, st);
 }
 
 int mmb_polar_to_cart(int32_t B, int32_t A, int32_t R, int32_t width, int32_t dtype, int32_t scan_u8,

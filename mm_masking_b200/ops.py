@@ -252,14 +252,18 @@ def _(mask, pts, cart_res):
 
 @torch.library.custom_op("mmb::sample_weights_bwd", mutates_args=(), device_types="cuda")
 def sample_weights_bwd(grad_w: Tensor, pts: Tensor, H: int, W: int, cart_res: float) -> Tensor:
-    """adjoint of mmb::sample_weights with respect to the mask: (N,n) -> (N,H,W)"""
+    """adjoint of mmb::sample_weights with respect to the mask: (N,n) -> (N,H,W).  Deterministic: the taps are
+    sorted by pixel and summed in tap order (mmb_sample_weights_bwd_det), no floating-point atomics"""
     lib = _capi.load_library()
     g, q = grad_w.contiguous(), pts.contiguous()
     N = g.shape[0]
     with torch.cuda.device(g.device):
         gm = torch.zeros((N, H, W), dtype=g.dtype, device=g.device)
-        _capi.check(lib.mmb_sample_weights_bwd(N, q.shape[1], q.shape[2], H, W, _DT[g.dtype], float(cart_res), _capi.ptr(g),
-                                               _capi.ptr(q), _capi.ptr(gm), _capi.stream_ptr()), "mmb_sample_weights_bwd")
+        ws_bytes = lib.mmb_sample_weights_bwd_det_workspace_bytes(N, q.shape[1], H, W, _DT[g.dtype])
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=g.device)
+        _capi.check(lib.mmb_sample_weights_bwd_det(N, q.shape[1], q.shape[2], H, W, _DT[g.dtype], float(cart_res),
+                                                   _capi.ptr(g), _capi.ptr(q), _capi.ptr(gm), _capi.ptr(ws), ws_bytes,
+                                                   _capi.stream_ptr()), "mmb_sample_weights_bwd_det")
     return gm
 
 

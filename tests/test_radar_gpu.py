@@ -197,3 +197,33 @@ def test_kstrongest_hand_worked_rows():
     assert rows[0].tolist() == [0, 0, 0, 2] and bins[0].tolist() == [200, 100, 300, 700]
     rho = np.float32(200) * np.float32(RES) - 0.31
     np.testing.assert_allclose(pts[0][0].cpu().numpy(), [rho, 0.0, 0.0], atol=1e-5)
+
+
+def test_mask_gradient_is_deterministic_and_matches_the_atomic_form():
+    """the adjoint of the weight sampler sums colliding taps in tap order (sort by pixel, no
+    floating-point atomics): two runs give identical bits, and the values equal the atomic kernel's up to
+    summation order.  Half of the points are exact duplicates, so many pixels receive several taps."""
+    import ctypes as C
+    from mm_masking_b200 import _capi
+    g = torch.Generator().manual_seed(8)
+    N, n, W = 3, 4000, 640
+    pts = torch.zeros((N, n, 3))
+    pts[:, :, :2] = (torch.rand((N, n, 2), generator=g) - 0.5) * 40          # dense: ~170 x 170 pixels for 4000 points
+    pts[:, n // 2:] = pts[:, :n // 2]
+    pts[:, :5] = 0.0                                                          # padding rows
+    pts = pts.cuda()
+    gw = torch.randn((N, n), generator=g).cuda()
+    a = torch.ops.mmb.sample_weights_bwd(gw, pts, W, W, 0.2384)
+    b = torch.ops.mmb.sample_weights_bwd(gw, pts, W, W, 0.2384)
+    assert torch.equal(a, b)
+    lib = _capi.load_library()
+    ref = torch.zeros((N, W, W), device="cuda")
+    _capi.check(lib.mmb_sample_weights_bwd(N, n, 3, W, W, _capi.F32, 0.2384, _capi.ptr(gw), _capi.ptr(pts), _capi.ptr(ref),
+                                           _capi.stream_ptr()), "atomic form")
+    assert (a != 0).sum() > 1000
+    np.testing.assert_allclose(a.cpu().numpy(), ref.cpu().numpy(), rtol=0, atol=2e-5)
+    # through autograd, against the oracle's adjoint
+    mask = torch.rand((N, W, W), generator=g).cuda().requires_grad_(True)
+    w = torch.ops.mmb.sample_weights(mask, pts, 0.2384)
+    (w * gw).sum().backward()
+    assert torch.equal(mask.grad, a)
