@@ -352,26 +352,176 @@ struct CfarArgs {
   int diff;
 };
 
-// Stage x[lo, hi) as an inclusive fp64 prefix sum: pre[0] = 0, pre[i + 1] = x[lo] + ... + x[lo + i].
+// byte -> fp32 value table of load_radar (radar_utils.py:20-27: byte / 255 in fp32), built once per block so that
+// the decode is one shared-memory load instead of an IEEE division per element
+#define MMB_L1(i) ((float)(i) / 255.0f)
+#define MMB_L4(i) MMB_L1(i), MMB_L1((i) + 1), MMB_L1((i) + 2), MMB_L1((i) + 3)
+#define MMB_L16(i) MMB_L4(i), MMB_L4((i) + 4), MMB_L4((i) + 8), MMB_L4((i) + 12)
+#define MMB_L64(i) MMB_L16(i), MMB_L16((i) + 16), MMB_L16((i) + 32), MMB_L16((i) + 48)
+// fl32(i / 255), the division done once by the compiler in IEEE single precision
+__device__ const float g_byte_lut[256] = {MMB_L64(0), MMB_L64(64), MMB_L64(128), MMB_L64(192)};
+__device__ __forceinline__ void build_byte_lut(float* lut) {
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) lut[i] = g_byte_lut[i];
+}
+// element (row, col) of the scan; u8 rows go through the table
 template <typename T>
-__device__ __forceinline__ void stage_prefix(const Scan<T>& sc, size_t row, int lo, int hi, double* pre, double* wt) {
+__device__ __forceinline__ T scan_value(const Scan<T>& sc, const float* lut, size_t row, int col) {
+  if (sc.kind == IN_U8) return (T)lut[static_cast<const uint8_t*>(sc.base)[row * sc.row_stride + 11 + col]];
+  return sc.at(row, col);
+}
+
+// The prefix array lives in shared memory with one pad double after every 8 (logical i -> i + i / 8): the staging
+// threads own 8 consecutive elements each (stride 9 doubles across the lanes: every bank once per half-warp), and
+// the window lookups of consecutive columns stay within three wavefronts.  Unpadded, the 64-byte lane stride of
+// the staging and the 32-byte stride of a four-column-per-thread lookup saturated the shared-memory pipe
+// (profiles/r02_radar_ncu_summary.md: 3.8x the ideal wavefronts, LSU data pipe 95 % busy).
+__host__ __device__ __forceinline__ int pidx(int i) { return i + (i >> 3); }
+__host__ __device__ __forceinline__ size_t prefix_bytes(int entries) { return (size_t)(pidx(entries) + 2) * sizeof(double); }
+
+// Stage x[lo, hi) as an inclusive fp64 prefix sum: pre[0] = 0, pre[i + 1] = x[lo] + ... + x[lo + i] (logical indices).
+// Every thread takes 8 consecutive elements, scans them in registers, and one block scan of the thread totals
+// supplies the offsets.  For uint8-derived scans every partial sum is exact in fp64 (the values are multiples of
+// 2^-32 below 1), so the prefix does not depend on this blocking.
+// `pad` entries after pre[len] repeat the total, so that a window that runs past hi (a slice truncated at the row
+// end in the reference) needs no index clamp.
+template <typename T>
+__device__ __forceinline__ void stage_prefix(const Scan<T>& sc, const float* lut, size_t row, int lo, int hi, double* pre,
+                                             double* wt, int pad = 0) {
   const int len = hi - lo;
-  for (int i = threadIdx.x; i < len; i += blockDim.x) pre[i + 1] = (double)sc.at(row, lo + i);
+  double carry = 0.0;
+  const uint8_t* pb = static_cast<const uint8_t*>(sc.base) + row * sc.row_stride + 11 + lo;
+  const float* pf = static_cast<const float*>(sc.base) + row * sc.row_stride + lo;
+  const double* pd = static_cast<const double*>(sc.base) + row * sc.row_stride + lo;
+  for (int base = 0; base < len; base += 8 * (int)blockDim.x) {
+    const int s = base + 8 * (int)threadIdx.x;
+    double v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = 0.0;
+    if (s < len) {
+      if (sc.kind == IN_U8) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) if (s + k < len) v[k] = (double)lut[pb[s + k]];
+      } else if (sc.kind == IN_F32) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) if (s + k < len) v[k] = (double)pf[s + k];
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) if (s + k < len) v[k] = pd[s + k];
+      }
+#pragma unroll
+      for (int k = 1; k < 8; ++k) v[k] += v[k - 1];
+    }
+    double total;
+    const double off = block_exclusive_scan<double>(v[7], wt, total) + carry;
+    if (s < len) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (s + k < len) pre[pidx(s + k + 1)] = v[k] + off;
+    }
+    carry += total;
+  }
   if (threadIdx.x == 0) pre[0] = 0.0;
+  for (int i = threadIdx.x; i < pad; i += blockDim.x) pre[pidx(len + 1 + i)] = carry;
   __syncthreads();
-  const int chunk = (len + blockDim.x - 1) / blockDim.x;
-  const int s = threadIdx.x * chunk, e = min(s + chunk, len);
-  double sum = 0.0;
-  for (int i = s; i < e; ++i) sum += pre[i + 1];
-  double total;
-  double run = block_exclusive_scan<double>(sum, wt, total);
-  for (int i = s; i < e; ++i) { run += pre[i + 1]; pre[i + 1] = run; }
+}
+
+// Forward, the shipped form: one thread per output pixel does the scans of a batch group one after the other.
+// What depends only on the pixel -- its range / angle, u = (range - res/2) / res and the normalised gx (:288,:322) --
+// is evaluated once per thread instead of once per scan; the searchsorted of the wobble fix starts from the index a
+// uniform azimuth spacing would give and walks to the exact answer (one or two comparisons for encoder jitter,
+// correct for any sorted table); raw Navtech bytes are decoded through a 256-entry table in shared memory instead of
+// an IEEE division per tap.  Every operation that produces a value is the same rounded operation, in the same
+// order, as in the one-scan kernel above (which the adjoint still uses), so the outputs are bit-identical.
+constexpr int POLAR_BGROUP = 8;
+template <typename T>
+__global__ void __launch_bounds__(ROW_THREADS) polar_to_cart_fwd_kernel(PolarArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  T* saz_all = reinterpret_cast<T*>(smem_raw);                 // (nb, A)
+  __shared__ float lut[256];
+  const int b0 = blockIdx.y * POLAR_BGROUP, nb = min(POLAR_BGROUP, a.B - b0);
+  const T* az = static_cast<const T*>(a.azimuths) + (size_t)b0 * a.A;
+  for (int i = threadIdx.x; i < nb * a.A; i += blockDim.x) saz_all[i] = az[i];
+  if (a.scan_kind == IN_U8) build_byte_lut(lut);
   __syncthreads();
+
+  const int npix = a.width * a.width;
+  const int tiles_x = (a.width + 15) >> 4;
+  const int px = (blockIdx.x % tiles_x) * 16 + (threadIdx.x & 15);
+  const int py = (blockIdx.x / tiles_x) * 16 + (threadIdx.x >> 4);
+  if (px >= a.width || py >= a.width) return;
+  const int pix = py * a.width + px;
+  const T range = static_cast<const T*>(a.range_tab)[pix];
+  const T angle = static_cast<const T*>(a.angle_tab)[pix];
+  const T res = (T)a.radar_res, half = (T)(a.radar_res / 2);
+  T u = div_rn(add_rn(range, -half), res);                                   // :288
+  if (u < (T)0) u = (T)0;                                                    // :314
+  const T gx = add_rn(mul_rn(div_rn(u, (T)(a.R - 1)), (T)2), (T)-1);         // :322
+  const int H = a.interpolate_crossover ? a.A + 2 : a.A;
+  // the x half of bilinear_taps (same operations): column, its two weights, which of the two columns exist
+  const T ix = mul_rn(add_rn(gx, (T)1), (T)(a.R - 1) / (T)2);
+  const T xw = t_floor(ix);
+  const T wx = add_rn(ix, -xw), ex = add_rn((T)1, -wx);
+  const int x0 = (int)fmax(fmin((double)xw, 2.0e9), -2.0e9);
+  const bool x0ok = x0 >= 0 && x0 < a.R, x1ok = x0 + 1 >= 0 && x0 + 1 < a.R;
+  const T hy = (T)(H - 1) / (T)2;
+  int guess = (int)((float)angle * ((float)a.A * 0.15915494f));             // angle / (2 pi / A): a starting point only
+  guess = min(max(guess, 0), a.A);
+  const bool u8 = a.scan_kind == IN_U8;
+  const size_t scan_stride = (size_t)a.A * a.scan_row_stride;
+  const uint8_t* sb = static_cast<const uint8_t*>(a.scan) + (size_t)b0 * scan_stride + 11;
+  const T* st = static_cast<const T*>(a.scan) + (size_t)b0 * scan_stride;
+  const int rs = (int)a.scan_row_stride;
+
+  for (int bb = 0; bb < nb; ++bb, sb += scan_stride, st += scan_stride) {
+    const T* saz = saz_all + bb * a.A;
+    T v;
+    if (a.fix_wobble) {
+      int c3 = guess;                        // searchsorted, side = left: first i with az[i] >= angle
+      while (c3 > 0 && !(saz[c3 - 1] < angle)) --c3;
+      while (c3 < a.A && saz[c3] < angle) ++c3;
+      if (c3 == a.A) c3 -= 1;                                                // :300
+      int c2 = c3 - 1;
+      if (c2 < 0) c2 += 1;                                                   // :302
+      const T a3 = saz[c3], a2 = saz[c2];
+      const T diff = add_rn(angle, -a3);
+      T num = mul_rn(diff, diff < (T)0 ? (T)1 : (T)0);
+      num = mul_rn(num, c3 > 0 ? (T)1 : (T)0);
+      const T delta = div_rn(num, add_rn(add_rn(a3, -a2), (T)1e-14));        // :308
+      v = add_rn((T)c3, delta);
+    } else {
+      const T step = div_rn(add_rn(saz[a.A - 1], -saz[0]), (T)(a.A - 1));    // :286
+      v = div_rn(add_rn(angle, -saz[0]), step);                              // :290
+    }
+    if (a.interpolate_crossover) v = add_rn(v, (T)1);                        // :317-319
+    const T gy = add_rn(mul_rn(div_rn(v, (T)(H - 1)), (T)2), (T)-1);         // :323
+    // the y half of bilinear_taps
+    const T iy = mul_rn(add_rn(gy, (T)1), hy);
+    const T yn = t_floor(iy);
+    const T ny = add_rn(iy, -yn), sy = add_rn((T)1, -ny);
+    const int y0 = (int)fmax(fmin((double)yn, 2.0e9), -2.0e9);
+    // rows of the (wrap-padded) scan behind y0 and y0 + 1, or -1
+    auto scan_row = [&](int y) -> int {
+      if (y < 0 || y >= H) return -1;
+      if (!a.interpolate_crossover) return y;
+      return y == 0 ? a.A - 1 : (y == a.A + 1 ? 0 : y - 1);                  // wrapped pad rows
+    };
+    const int r0 = scan_row(y0), r1 = scan_row(y0 + 1);
+    auto tap = [&](int r, bool xok, int x) -> T {
+      if (r < 0 || !xok) return (T)0;
+      const int o = r * rs + x;
+      return u8 ? (T)lut[sb[o]] : st[o];
+    };
+    T acc = mul_rn(tap(r0, x0ok, x0), mul_rn(sy, ex));
+    acc = add_rn(acc, mul_rn(tap(r0, x1ok, x0 + 1), mul_rn(sy, wx)));
+    acc = add_rn(acc, mul_rn(tap(r1, x0ok, x0), mul_rn(ny, ex)));
+    acc = add_rn(acc, mul_rn(tap(r1, x1ok, x0 + 1), mul_rn(ny, wx)));
+    static_cast<T*>(a.out)[(size_t)(b0 + bb) * npix + pix] = acc;
+  }
 }
 
 __device__ __forceinline__ double cfar_threshold_at(const CfarArgs& a, const double* pre, int j) {
   if (j < a.mincol || j >= a.maxcol) return 1000.0;
-  auto P = [&](int k) { return pre[min(k, a.hi) - a.lo]; };     // slices past the row end are truncated
+  auto P = [&](int k) { return pre[pidx(min(k, a.hi) - a.lo)]; };     // slices past the row end are truncated
   const double left = P(j - a.guard) - P(j - a.w2 - a.guard);
   const double right = P(j + a.w2 + a.guard + 1) - P(j + a.guard + 1);
   return a.a_thresh * (fmax(left, right) / (double)a.w2) + a.b_thresh;
@@ -384,14 +534,73 @@ __device__ __forceinline__ T cfar_mask_value(const CfarArgs& a, T x, double thre
   return (soft > (T)0.99 || soft < (T)-0.99) ? soft : (T)0;                              // hardshrink :65
 }
 
+// Non-differentiable mask bit x > thres (radar_utils.py:67).  The window sums come from the prefix; the threshold is
+// first formed without the fp64 division (one fma with a / w2), and only when x lies within 1e-12 (1 + |t|) of it --
+// far outside the rounding of either form -- is the reference's own expression evaluated: same bits, no division on
+// the common path.
+__device__ __forceinline__ bool cfar_hard_bit(const CfarArgs& a, const double* pre, int j, double x, double a_over_w2) {
+  auto P = [&](int k) { return pre[pidx(min(k, a.hi) - a.lo)]; };
+  const double left = P(j - a.guard) - P(j - a.w2 - a.guard);
+  const double right = P(j + a.w2 + a.guard + 1) - P(j + a.guard + 1);
+  const double t = fma(fmax(left, right), a_over_w2, a.b_thresh);
+  if (fabs(x - t) > 1.0e-12 * (1.0 + fabs(t))) return x > t;
+  return x > a.a_thresh * (fmax(left, right) / (double)a.w2) + a.b_thresh;
+}
+
+// !diff: float mask, four columns per thread, 16-byte stores; columns outside [mincol, maxcol) are zero and read
+// nothing.  The prefix is padded past hi (see stage_prefix), so the window ends need no clamp.
+template <typename T>
+__global__ void __launch_bounds__(ROW_THREADS, 8) cfar_mask_hard_kernel(CfarArgs a) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  double* pre = reinterpret_cast<double*>(smem_raw);
+  __shared__ double wt[33];
+  __shared__ float lut[256];
+  const size_t row = blockIdx.x;
+  Scan<T> sc; sc.base = a.scan; sc.kind = a.scan_kind; sc.row_stride = a.scan_row_stride;
+  if (a.scan_kind == IN_U8) { build_byte_lut(lut); __syncthreads(); }
+  const int pad = a.w2 + a.guard + 2;
+  stage_prefix<T>(sc, lut, row, a.lo, a.hi, pre, wt, pad);
+  const double aw = a.a_thresh / (double)a.w2, bt = a.b_thresh;
+  const uint8_t* pb = static_cast<const uint8_t*>(sc.base) + row * sc.row_stride + 11;
+  const T* pt = static_cast<const T*>(sc.base) + row * sc.row_stride;
+  const bool u8 = a.scan_kind == IN_U8;
+  // window ends relative to column j, as indices into pre (which starts at column lo)
+  const int oA = -a.guard - a.lo, oB = -a.w2 - a.guard - a.lo, oC = a.w2 + a.guard + 1 - a.lo, oD = a.guard + 1 - a.lo;
+  float* out = static_cast<float*>(a.mask) + row * a.R;
+  // zeros outside [mincol, maxcol): 16-byte stores where the row allows it
+  if ((a.R & 3) == 0) {
+    const int z0 = (a.mincol >> 2) << 2, z1 = ((a.maxcol + 3) >> 2) << 2;      // quads fully outside the window
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int j = 4 * threadIdx.x; j < z0; j += 4 * blockDim.x) *reinterpret_cast<float4*>(out + j) = zero;
+    for (int j = z1 + 4 * threadIdx.x; j < a.R; j += 4 * blockDim.x) *reinterpret_cast<float4*>(out + j) = zero;
+    for (int j = z0 + threadIdx.x; j < a.mincol; j += blockDim.x) out[j] = 0.f;
+    for (int j = a.maxcol + threadIdx.x; j < min(z1, a.R); j += blockDim.x) out[j] = 0.f;
+  } else {
+    for (int j = threadIdx.x; j < a.mincol; j += blockDim.x) out[j] = 0.f;
+    for (int j = a.maxcol + threadIdx.x; j < a.R; j += blockDim.x) out[j] = 0.f;
+  }
+  // one column per lane: consecutive lanes read consecutive prefix entries and write consecutive floats
+  for (int j = a.mincol + threadIdx.x; j < a.maxcol; j += blockDim.x) {
+    const double left = pre[pidx(j + oA)] - pre[pidx(j + oB)], right = pre[pidx(j + oC)] - pre[pidx(j + oD)];
+    const double mx = fmax(left, right);
+    const double t = fma(mx, aw, bt);
+    const double x = u8 ? (double)lut[pb[j]] : (double)pt[j];
+    bool one = x > t;
+    if (fabs(x - t) <= 1.0e-12 * (1.0 + fabs(t))) one = x > a.a_thresh * (mx / (double)a.w2) + bt;   // the reference's own form
+    out[j] = one ? 1.f : 0.f;
+  }
+}
+
 template <typename T, bool DIFF>
 __global__ void __launch_bounds__(ROW_THREADS) cfar_mask_kernel(CfarArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* pre = reinterpret_cast<double*>(smem_raw);
   __shared__ double wt[33];
   const size_t row = blockIdx.x;
+  __shared__ float lut[256];
   Scan<T> sc; sc.base = a.scan; sc.kind = a.scan_kind; sc.row_stride = a.scan_row_stride;
-  stage_prefix<T>(sc, row, a.lo, a.hi, pre, wt);
+  if (a.scan_kind == IN_U8) { build_byte_lut(lut); __syncthreads(); }
+  stage_prefix<T>(sc, lut, row, a.lo, a.hi, pre, wt);
   typedef typename std::conditional<DIFF, T, float>::type OT;
   OT* out = static_cast<OT*>(a.mask) + row * a.R;
   for (int j = threadIdx.x; j < a.R; j += blockDim.x) {
@@ -439,13 +648,18 @@ __host__ __device__ __forceinline__ void peak_span(const PeakArgs& a, bool fused
 template <typename T, bool FUSED>
 __device__ __forceinline__ void stage_arr(const PeakArgs& a, size_t row, T* arr, double* pre, double* wt) {
   if (FUSED) {
+    __shared__ float lut[256];
     Scan<T> sc; sc.base = a.cfar.scan; sc.kind = a.cfar.scan_kind; sc.row_stride = a.cfar.scan_row_stride;
-    stage_prefix<T>(sc, row, a.cfar.lo, a.cfar.hi, pre, wt);
+    if (a.cfar.scan_kind == IN_U8) { build_byte_lut(lut); __syncthreads(); }
+    stage_prefix<T>(sc, lut, row, a.cfar.lo, a.cfar.hi, pre, wt);
+    const double aw = a.cfar.a_thresh / (double)a.cfar.w2;
     const int k0 = max(a.cfar.mincol - 1, 0), k1 = min(a.cfar.maxcol + 1, a.R);   // arr is read on [mincol-1, maxcol]
     for (int k = k0 + threadIdx.x; k < k1; k += blockDim.x) {
       T m = (T)0;
       if (k >= a.cfar.mincol && k < a.cfar.maxcol) {
-        m = cfar_mask_value<T>(a.cfar, sc.at(row, k), cfar_threshold_at(a.cfar, pre, k));
+        const T x = scan_value<T>(sc, lut, row, k);
+        if (a.cfar.diff) m = cfar_mask_value<T>(a.cfar, x, cfar_threshold_at(a.cfar, pre, k));
+        else m = cfar_hard_bit(a.cfar, pre, k, (double)x, aw) ? (T)1 : (T)0;
       }
       arr[k] = mul_rn((T)__fmul_rn(a.res, (float)k), m);
     }
@@ -475,7 +689,7 @@ template <typename T, bool FUSED>
 __global__ void __launch_bounds__(ROW_THREADS) peak_rows_kernel(PeakArgs a) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   double* pre = reinterpret_cast<double*>(smem_raw);                       // fused source only
-  T* arr = reinterpret_cast<T*>(smem_raw + (FUSED ? (size_t)(a.cfar.hi - a.cfar.lo + 1) * sizeof(double) : 0));
+  T* arr = reinterpret_cast<T*>(smem_raw + (FUSED ? prefix_bytes(a.cfar.hi - a.cfar.lo + 1) : 0));
   __shared__ double wt[33];
   __shared__ int wi[33];
   const size_t row = blockIdx.x;
@@ -581,65 +795,88 @@ __device__ __forceinline__ unsigned int ordered_bits(float v) {
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
-__global__ void __launch_bounds__(ROW_THREADS) kstrong_rows_kernel(KStrongArgs a) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  float* val = reinterpret_cast<float*>(smem_raw);
-  __shared__ double wd[33];
-  __shared__ unsigned long long wk[33];
-  const size_t row = blockIdx.x;
-  Scan<float> sc; sc.base = a.scan; sc.kind = a.scan_kind; sc.row_stride = a.scan_row_stride;
+// One WARP per azimuth row, KSTRONG_WARPS rows per block, no block-wide synchronisation inside the selection.
+//   pass 1: the lanes stride over the row's bins (bytes decoded through the shared table), summing in fp64 -- the
+//           mean of detector.inl:57-61, exact for uint8-derived scans whatever the order;
+//   pass 2: the bins at or above the threshold are compacted (ballot) into the warp's list of 64-bit keys
+//           (ordered value bits || inverted bin index), in bin order, up to KSTRONG_LIST entries;
+//   pass 3: k rounds of a warp-wide maximum over the list (two 32-bit REDUX), the winner is cleared.
+//   A row with more candidates than the list holds (a saturated row) is selected without storage instead: round r
+//   takes the largest key below the key of round r - 1, re-reading the row (L1-resident) every round.
+// Order within a row: descending value, ties to the lower bin -- the choice the literal reference leaves open
+// (tests/kstrong_pin.py).
+constexpr int KSTRONG_WARPS = 8;
+constexpr int KSTRONG_LIST = 256;
+__global__ void __launch_bounds__(KSTRONG_WARPS * 32) kstrong_rows_kernel(KStrongArgs a) {
+  __shared__ unsigned long long keys_all[KSTRONG_WARPS][KSTRONG_LIST];
+  __shared__ float lut[256];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int len = a.j1 - a.j0;
+  unsigned long long* keys = keys_all[warp];
+  if (a.scan_kind == IN_U8) build_byte_lut(lut);
+  __syncthreads();
+  const size_t row = (size_t)blockIdx.x * KSTRONG_WARPS + warp;
+  if (row >= (size_t)a.rows) return;                        // whole warp
+  const bool u8 = a.scan_kind == IN_U8;
+  const uint8_t* pb = static_cast<const uint8_t*>(a.scan) + row * a.scan_row_stride + 11 + a.j0;
+  const float* pf = static_cast<const float*>(a.scan) + row * a.scan_row_stride + a.j0;
+  auto value = [&](int i) -> float { return u8 ? lut[pb[i]] : pf[i]; };
+  auto key_of = [&](float v, int i) -> unsigned long long {
+    return ((unsigned long long)ordered_bits(v) << 32) | (unsigned int)(0x7fffffff - i);
+  };
   double sum = 0.0;
-  for (int i = threadIdx.x; i < len; i += blockDim.x) {
-    const float v = sc.at(row, a.j0 + i);
-    val[i] = v;
-    sum += (double)v;
-  }
+  for (int i = lane; i < len; i += 32) sum += (double)value(i);
   sum = warp_sum(sum);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
-  if (lane == 0) wd[warp] = sum;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double s = 0.0;
-    for (int w = 0; w < nwarp; ++w) s += wd[w];
-    wd[32] = (s / a.N) * a.t2 + a.t3;
+  const double thres = (sum / a.N) * a.t2 + a.t3;
+  int cnt = 0;
+  for (int base = 0; base < len; base += 32) {
+    const int i = base + lane;
+    const float v = i < len ? value(i) : 0.f;
+    const bool pass = i < len && (double)v >= thres;
+    const unsigned m = __ballot_sync(0xffffffffu, pass);
+    const int at = cnt + __popc(m & ((1u << lane) - 1u));
+    if (pass && at < KSTRONG_LIST) keys[at] = key_of(v, i);
+    cnt += __popc(m);
   }
-  __syncthreads();
-  const double thres = wd[32];
-
+  __syncwarp();
   int taken = 0;
-  for (int round = 0; round < a.k; ++round) {
-    unsigned long long best = 0ull;
-    for (int i = threadIdx.x; i < len; i += blockDim.x) {
-      const float v = val[i];
-      if ((double)v >= thres) {
-        const unsigned long long key = ((unsigned long long)ordered_bits(v) << 32) | (unsigned int)(0x7fffffff - i);
-        best = key > best ? key : best;
+  if (cnt <= KSTRONG_LIST) {
+    for (int round = 0; round < a.k && round < cnt; ++round) {
+      unsigned long long best = 0ull; int where = -1;
+      for (int i = lane; i < cnt; i += 32) {
+        const unsigned long long key = keys[i];
+        if (key > best) { best = key; where = i; }
       }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const unsigned long long y = __shfl_xor_sync(0xffffffffu, best, o);
-      best = y > best ? y : best;
-    }
-    if (lane == 0) wk[warp] = best;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      unsigned long long bb = 0ull;
-      for (int w = 0; w < nwarp; ++w) bb = wk[w] > bb ? wk[w] : bb;
-      wk[32] = bb;
-      if (bb) {
-        const int i = 0x7fffffff - (int)(bb & 0xffffffffu);
-        a.sel_bin[row * a.k + round] = a.j0 + i;
-        val[i] = -__builtin_huge_valf();          // taken; -inf never passes `>= thres`
+      const unsigned hi = (unsigned)(best >> 32), lo = (unsigned)best;
+      const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
+      const unsigned mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? lo : 0u);
+      if (hi == mhi && lo == mlo && where >= 0) {            // keys are unique: exactly one lane
+        keys[where] = 0ull;
+        a.sel_bin[row * a.k + round] = a.j0 + (0x7fffffff - (int)mlo);
       }
+      ++taken;
+      __syncwarp();
     }
-    __syncthreads();
-    if (!wk[32]) break;
-    ++taken;
-    __syncthreads();
+  } else {
+    unsigned long long prev = ~0ull;
+    for (int round = 0; round < a.k && round < cnt; ++round) {
+      unsigned long long best = 0ull;
+      for (int i = lane; i < len; i += 32) {
+        const float v = value(i);
+        if ((double)v >= thres) {
+          const unsigned long long key = key_of(v, i);
+          if (key < prev && key > best) best = key;
+        }
+      }
+      const unsigned hi = (unsigned)(best >> 32), lo = (unsigned)best;
+      const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
+      const unsigned mlo = __reduce_max_sync(0xffffffffu, hi == mhi ? lo : 0u);
+      prev = ((unsigned long long)mhi << 32) | mlo;
+      if (lane == 0) a.sel_bin[row * a.k + round] = a.j0 + (0x7fffffff - (int)mlo);
+      ++taken;
+    }
   }
-  if (threadIdx.x == 0) a.counts[row] = taken;
+  if (lane == 0) a.counts[row] = taken;
 }
 
 template <typename T>
@@ -723,7 +960,7 @@ static ExtractWs carve_extract(void* base, int B, int A, int rowcap, size_t elt)
 template <typename T, bool FUSED>
 static int launch_peak_rows(const PeakArgs& a, cudaStream_t st) {
   size_t smem = (size_t)a.R * sizeof(T) + 16;
-  if (FUSED) smem += (size_t)(a.cfar.hi - a.cfar.lo + 1) * sizeof(double);
+  if (FUSED) smem += prefix_bytes(a.cfar.hi - a.cfar.lo + 1);
   int rc = opt_in_smem(peak_rows_kernel<T, FUSED>, smem);
   if (rc) return rc;
   peak_rows_kernel<T, FUSED><<<a.rows, ROW_THREADS, smem, st>>>(a);
@@ -912,16 +1149,17 @@ int mmb_polar_to_cart(int32_t B, int32_t A, int32_t R, int32_t width, int32_t dt
   a.radar_res = radar_res;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int tiles = (width + 15) / 16;
-  dim3 grid(tiles * tiles, B);
+  dim3 grid(tiles * tiles, (B + POLAR_BGROUP - 1) / POLAR_BGROUP);
+  const int nbmax = B < POLAR_BGROUP ? B : POLAR_BGROUP;
   int rc;
   if (dtype == MMB_F32) {
-    const size_t smem = (size_t)A * sizeof(float);
-    if ((rc = opt_in_smem(polar_to_cart_kernel<float, false>, smem))) return rc;
-    polar_to_cart_kernel<float, false><<<grid, ROW_THREADS, smem, st>>>(a);
+    const size_t smem = (size_t)nbmax * A * sizeof(float);
+    if ((rc = opt_in_smem(polar_to_cart_fwd_kernel<float>, smem))) return rc;
+    polar_to_cart_fwd_kernel<float><<<grid, ROW_THREADS, smem, st>>>(a);
   } else {
-    const size_t smem = (size_t)A * sizeof(double);
-    if ((rc = opt_in_smem(polar_to_cart_kernel<double, false>, smem))) return rc;
-    polar_to_cart_kernel<double, false><<<grid, ROW_THREADS, smem, st>>>(a);
+    const size_t smem = (size_t)nbmax * A * sizeof(double);
+    if ((rc = opt_in_smem(polar_to_cart_fwd_kernel<double>, smem))) return rc;
+    polar_to_cart_fwd_kernel<double><<<grid, ROW_THREADS, smem, st>>>(a);
   }
   return check_launch();
 }
@@ -943,14 +1181,21 @@ int mmb_cfar_mask(const mmb_cfar_params* p, const void* scan, void* mask, void* 
   if (!scan || !mask) return MMB_ERR_NULL_POINTER;
   c.mask = mask;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const size_t smem = (size_t)(c.hi - c.lo + 1) * sizeof(double);
+  const size_t smem = prefix_bytes(c.hi - c.lo + 1);
 #define MMB_CFAR_LAUNCH(T, D)                                                  \
   do {                                                                         \
     if ((rc = opt_in_smem(cfar_mask_kernel<T, D>, smem))) return rc;           \
     cfar_mask_kernel<T, D><<<c.rows, ROW_THREADS, smem, st>>>(c);              \
   } while (0)
-  if (p->dtype == MMB_F32) { if (c.diff) MMB_CFAR_LAUNCH(float, true); else MMB_CFAR_LAUNCH(float, false); }
-  else { if (c.diff) MMB_CFAR_LAUNCH(double, true); else MMB_CFAR_LAUNCH(double, false); }
+#define MMB_CFAR_HARD(T)                                                       \
+  do {                                                                         \
+    const size_t smem_h = prefix_bytes(c.hi - c.lo + 1 + c.w2 + c.guard + 2);   \
+    if ((rc = opt_in_smem(cfar_mask_hard_kernel<T>, smem_h))) return rc;       \
+    cfar_mask_hard_kernel<T><<<c.rows, ROW_THREADS, smem_h, st>>>(c);          \
+  } while (0)
+  if (p->dtype == MMB_F32) { if (c.diff) MMB_CFAR_LAUNCH(float, true); else MMB_CFAR_HARD(float); }
+  else { if (c.diff) MMB_CFAR_LAUNCH(double, true); else MMB_CFAR_HARD(double); }
+#undef MMB_CFAR_HARD
 #undef MMB_CFAR_LAUNCH
   return check_launch();
 }
@@ -1058,9 +1303,7 @@ int mmb_kstrong_select(const mmb_kstrong_params* p, const void* scan, void* work
   a.N = maxcol - mincol; a.t2 = p->threshold2; a.t3 = p->threshold3;
   a.sel_bin = w.sel_bin; a.counts = w.counts;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const size_t smem = (size_t)(a.j1 - a.j0 + 1) * sizeof(float);
-  if ((rc = opt_in_smem(kstrong_rows_kernel, smem))) return rc;
-  kstrong_rows_kernel<<<a.rows, ROW_THREADS, smem, st>>>(a);
+  kstrong_rows_kernel<<<(a.rows + KSTRONG_WARPS - 1) / KSTRONG_WARPS, KSTRONG_WARPS * 32, 0, st>>>(a);
   if ((rc = check_launch())) return rc;
   row_offsets_kernel<<<p->B, 256, 0, st>>>(w.counts, p->A, w.offsets, totals);
   return check_launch();

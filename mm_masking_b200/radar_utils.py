@@ -137,6 +137,9 @@ def cfar_mask(raw_scans, res, width=101, minr=2.0, maxr=80.0, guard=5, a_thresh=
     return mask if raw_scans.is_cuda else mask.to(raw_scans.device)
 
 
+_EXTRACT_CAPACITY = 32768        # points per scan written before the totals are known (radar scans give 2k-15k)
+
+
 def _extract(src, p, azimuth_angles, T_ab, out_device):
     """count -> allocate -> write; returns the list of (P_b,3) tensors."""
     lib = _capi.load_library()
@@ -151,16 +154,26 @@ def _extract(src, p, azimuth_angles, T_ab, out_device):
         totals = torch.empty(B, dtype=torch.int32, device=dev)
         _capi.check(lib.mmb_extract_count(p, _capi.ptr(src), _capi.ptr(ws), ws_bytes, _capi.ptr(totals),
                                           _capi.stream_ptr()), "mmb_extract_count")
-        tot = totals.cpu().tolist()                       # the one host sync: the output is a list of ragged clouds
+
+        def write(cap_entries):
+            ent_val = torch.empty((B, cap_entries), dtype=wdt, device=dev)
+            ent_row = torch.empty((B, cap_entries), dtype=torch.int32, device=dev)
+            out_pts = torch.empty((B, cap_entries // 2, 3), dtype=wdt, device=dev)
+            _capi.check(lib.mmb_extract_write(p, _capi.ptr(az), _capi.ptr(Tm), _capi.ptr(ws), ws_bytes, cap_entries,
+                                              _capi.ptr(ent_val), _capi.ptr(ent_row), cap_entries // 2, _capi.ptr(out_pts),
+                                              _capi.stream_ptr()), "mmb_extract_write")
+            return out_pts
+
+        # the points are written with a generous fixed capacity BEFORE the per-scan totals are read, so the one
+        # host synchronisation of the call (the output is a list of ragged clouds) sits at the very end instead of
+        # between the two launches; a scan with more points than the capacity is rewritten (not seen on radar data)
+        cap = 2 * _EXTRACT_CAPACITY
+        pts = write(cap)
+        tot = totals.cpu().tolist()
         if any(t % 2 for t in tot):
             raise ValueError("odd number of peak entries in a scan (a detection run touches the last range bin)")
-        cap = max(max(tot), 2)
-        ent_val = torch.empty((B, cap), dtype=wdt, device=dev)
-        ent_row = torch.empty((B, cap), dtype=torch.int32, device=dev)
-        pts = torch.empty((B, cap // 2, 3), dtype=wdt, device=dev)
-        _capi.check(lib.mmb_extract_write(p, _capi.ptr(az), _capi.ptr(Tm), _capi.ptr(ws), ws_bytes,
-                                          cap, _capi.ptr(ent_val), _capi.ptr(ent_row), cap // 2, _capi.ptr(pts),
-                                          _capi.stream_ptr()), "mmb_extract_write")
+        if max(tot) > cap:
+            pts = write(max(tot))
     out = [pts[b, :tot[b] // 2] for b in range(B)]
     return out if out_device == dev else [o.to(out_device) for o in out]
 
@@ -222,13 +235,13 @@ def kstrong_extract_pc(raw_scans, res, azimuth_angles, kstrong=12, threshold2=0.
         totals = torch.empty(B, dtype=torch.int32, device=dev)
         _capi.check(lib.mmb_kstrong_select(p, _capi.ptr(x), _capi.ptr(ws), ws_bytes, _capi.ptr(totals),
                                            _capi.stream_ptr()), "mmb_kstrong_select")
-        tot = totals.cpu().tolist()
-        cap = max(max(tot), 1)
+        cap = max(A * int(kstrong), 1)                    # the exact upper bound: no read of the totals before the write
         pts = torch.empty((B, cap, 3), dtype=wdt, device=dev)
         rows = torch.empty((B, cap), dtype=torch.int32, device=dev) if return_bins else None
         bins = torch.empty((B, cap), dtype=torch.int32, device=dev) if return_bins else None
         _capi.check(lib.mmb_kstrong_write(p, _capi.ptr(az), _capi.ptr(ws), ws_bytes, cap, _capi.ptr(pts),
                                           _capi.ptr(rows), _capi.ptr(bins), _capi.stream_ptr()), "mmb_kstrong_write")
+        tot = totals.cpu().tolist()                        # the one host sync, after both launches
     back = (lambda t: t) if raw_scans.is_cuda else (lambda t: t.to(raw_scans.device))
     out = [back(pts[b, :tot[b]]) for b in range(B)]
     if return_bins:

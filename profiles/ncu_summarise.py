@@ -27,6 +27,7 @@ def main():
     ap.add_argument("report")
     ap.add_argument("--queries", type=float, default=0, help="divide instruction counts by this (e.g. queries per launch)")
     ap.add_argument("--top", type=int, default=30)
+    ap.add_argument("--kernel", default="", help="substring of the kernel name whose source lines are listed (default: the first)")
     args = ap.parse_args()
     rows = list(csv.reader(io.StringIO(ncu(["-i", args.report, "--page", "raw", "--csv"]))))
     hdr, units = rows[0], rows[1]
@@ -42,11 +43,15 @@ def main():
     lines, cur, seen_fn = {}, None, 0
     total_inst = total_samp = 0
     col = None
+    active = False
     for r in src:
         if len(r) >= 2 and r[0] == "Function Name":
-            seen_fn += 1
-            if seen_fn > 1:
+            if active:
                 break
+            active = args.kernel in r[1]
+            col = None
+            continue
+        if not active:
             continue
         if len(r) > 8 and r[0] == "Line No":
             col = {name: i for i, name in enumerate(r)}

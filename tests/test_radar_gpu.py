@@ -174,7 +174,8 @@ def test_polar_to_cartesian_full_size_matches_oracle():
 def test_kstrongest_matches_oracle():
     sc = synth.make_radar_scans(B=2, seed=23)
     ru = _ru()
-    for kw in (dict(), dict(kstrong=3, threshold2=1.5, threshold3=0.1), dict(kstrong=40, minr=0.0, maxr=500.0)):
+    for kw in (dict(), dict(kstrong=3, threshold2=1.5, threshold3=0.1), dict(kstrong=40, minr=0.0, maxr=500.0),
+               dict(kstrong=20, threshold3=0.01)):          # most bins pass: more candidates than the shared list holds
         ref = RO.kstrongest(sc["fft"], sc["azimuths"], RES, **kw)
         pts, rows, bins = ru.kstrong_extract_pc(torch.from_numpy(sc["raw"]).cuda(), RES, torch.from_numpy(sc["azimuths"]).cuda(),
                                                 return_bins=True, **kw)
