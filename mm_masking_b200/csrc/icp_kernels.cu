@@ -1532,6 +1532,20 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
         walk(s0, e0);
       }
     };
+    // cold start, squares of at most 32 rows: only the non-empty row run nearest to the query's row is walked -- any
+    // target gives a bound, and the disc scan that follows is what makes the answer exact; walking the whole
+    // square would look at every wall inside it.  Returns false when the square is empty.
+    auto probe_square = [&](int x0, int x1, int ylo, int yhi, int cy) -> bool {
+      const int y = ylo + lane;
+      int s0 = 0, e0 = 0;
+      if (y <= yhi) { const int* rowp = start + y * GRID_G; s0 = __ldg(rowp + x0); e0 = __ldg(rowp + x1 + 1); }
+      const unsigned key = e0 > s0 ? ((unsigned)abs(y - cy) << 8) | (unsigned)lane : 0xffffffffu;
+      const unsigned best = __reduce_min_sync(0xffffffffu, key);
+      if (best == 0xffffffffu) return false;
+      const int c = (int)(best & 255u);
+      walk(lane == c ? s0 : 0, lane == c ? e0 : 0);
+      return true;
+    };
     // the outside bucket is one run, held by lane 0
     auto scan_outside = [&]() {
       walk(lane == 0 ? __ldg(start + GRID_OUTSIDE) : 0, lane == 0 ? __ldg(start + GRID_OUTSIDE + 1) : 0);
@@ -1566,8 +1580,12 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
       int rad = 1;
       for (;;) {
         const int x0 = max(cx - rad, 0), x1 = min(cx + rad, GRID_G - 1), y0 = max(cy - rad, 0), y1 = min(cy + rad, GRID_G - 1);
-        scan_square(x0, x1, y0, y1);
-        reduce();
+        if (y1 - y0 < 32) {
+          if (probe_square(x0, x1, y0, y1, cy)) { reduce(); break; }          // a bound, not yet the answer: done stays false
+        } else {
+          scan_square(x0, x1, y0, y1);
+          reduce();
+        }
         if (D2 < 1.0e300) {
           const double dc = sqrt_upper(D2) * sG[2] * (1.0 + SLACK) + abs_slack;   // cells, inflated
           const double gap = fmin(fmin(fx, (double)GRID_G - fx), fmin(fy, (double)GRID_G - fy));   // to the grid border
@@ -1851,7 +1869,7 @@ __device__ __forceinline__ const double* cluster_sum12(double (&acc)[12], double
 // k-1 needs is reduced across the cluster through distributed shared memory (cluster_sum12), and
 // every CTA repeats the tiny serial part (SO(3) adjoint + 3x3 / 6x6 solve) on identical inputs.
 template <typename T, int ICP, int DIM>
-__global__ void __launch_bounds__(BWD_THREADS) icp_backward_kernel(BwdArgs a) {
+__global__ void __launch_bounds__(BWD_THREADS, 2) icp_backward_kernel(BwdArgs a) {
   constexpr int D = Dof<DIM>::D;
   __shared__ double scratch[12 * (BWD_THREADS / 32 + 1)];
   __shared__ double part[2][12], tot12[12];
@@ -1913,6 +1931,7 @@ __global__ void __launch_bounds__(BWD_THREADS) icp_backward_kernel(BwdArgs a) {
   if (use_pre) {
     for (int idx = tid; idx < iters * D; idx += blockDim.x) {
       const int k = idx / D, c = idx % D;
+      if (!a.sv.active[(size_t)k * a.N + b]) continue;      // frozen in iteration k: its history slots were never written
       const double* As = a.sv.A_hist + ((size_t)k * a.N + b) * 36;
       double A[D * D], e[D], x[D];
       for (int q = 0; q < D * D; ++q) A[q] = As[q];

@@ -98,6 +98,16 @@ def pol_2_cart(pointcloud):
 # ---------------------------------------------------------------------------------------------
 # K2a: GO-CFAR mask and peak extraction
 # ---------------------------------------------------------------------------------------------
+def _warn_no_grad(t, what):
+    """The soft (diff=True) mask and peak extraction exist in the reference to be differentiated through; the CUDA
+    path implements their forward values only (the reference has no live diff=True call site).  A
+    caller who would back-propagate through them is told so instead of silently getting no gradient."""
+    if isinstance(t, torch.Tensor) and t.requires_grad and torch.is_grad_enabled():
+        import warnings
+        warnings.warn(f"mm_masking_b200.radar_utils.{what}: the input requires grad but this op is forward-only here; "
+                      "its output carries no autograd graph", RuntimeWarning, stacklevel=3)
+
+
 def _cfar_params(B, A, R, dtype, scan_u8, res, width, minr, maxr, guard, a_thresh, b_thresh, diff, steep_fact):
     p = _capi.CfarParams()
     p.B, p.A, p.R, p.dtype, p.scan_u8 = B, A, R, dtype, int(scan_u8)
@@ -128,6 +138,7 @@ def cfar_mask(raw_scans, res, width=101, minr=2.0, maxr=80.0, guard=5, a_thresh=
     otherwise.  Window sums are exact (fp64 prefix sums), see DESIGN.md section 6.
     """
     lib = _capi.load_library()
+    _warn_no_grad(raw_scans, "cfar_mask")
     x, dt, u8, B, A, R = _scan_args(raw_scans)
     p = _cfar_params(B, A, R, dt, u8, res, width, minr, maxr, guard, a_thresh, b_thresh, diff, steep_fact)
     out_dtype = (torch.float32 if u8 else x.dtype) if diff else torch.float32
@@ -184,6 +195,7 @@ def extract_pc(thres_mask, res, azimuth_angles, azimuth_times, T_ab=None, diff=T
     last range, azimuth-major, range ascending.  `azimuth_times` is accepted for call
     compatibility (the reference carries it through the averaging and then drops it)."""
     assert thres_mask.ndim == 3
+    _warn_no_grad(thres_mask, "extract_pc")
     dev = _device_of(thres_mask)
     wdt = torch.promote_types(thres_mask.dtype, azimuth_angles.dtype)
     if wdt not in _DT:
