@@ -63,6 +63,8 @@ def main():
                 cur = int(r[0])
             except ValueError:
                 continue
+            if "Instructions Executed" not in col or "# Samples" not in col:
+                continue
             inst = int(r[col["Instructions Executed"]] or 0)
             samp = int(r[col["# Samples"]] or 0)
             thr = int(r[col["Thread Instructions Executed"]] or 0)
