@@ -40,6 +40,8 @@ def algorithmic_bytes(B, n_points_total, n_k_points):
         "cfar_extract_fused_f32": B * (A * 1308 * 4) + n_points_total * 12,
         "extract_pc_from_mask": B * (A * R * 4) + n_points_total * 12,
         "kstrong_u8": B * (A * 1310 * 1) + n_k_points * 12,
+        "cfar_extract_op_u8": B * (A * 1308 * 1) + n_points_total * 12,
+        "kstrong_op_u8": B * (A * 1310 * 1) + n_k_points * 12,
         "sample_weights_fwd": B * 2000 * 28,
         "sample_weights_bwd": B * 2000 * 28,
     }
@@ -76,6 +78,7 @@ def run(args, local_rank=0):
     n_pts = sum(len(p) for p in pts_list)
     k_list = ru.kstrong_extract_pc(raw, RES, az)
     n_k = sum(len(p) for p in k_list)
+    cap_pts = max(len(p) for p in pts_list) + 16
     wmask = torch.rand((B, W, W), device=dev, requires_grad=True)
     spts = torch.zeros((B, 2000, 3), device=dev)
     spts[:, :, :2] = (torch.rand((B, 2000, 2), device=dev) - 0.5) * 150
@@ -96,6 +99,11 @@ def run(args, local_rank=0):
         "cfar_extract_fused_f32": lambda: ru.cfar_extract_pc(fft, RES, az),
         "extract_pc_from_mask": lambda: ru.extract_pc(mask, RES, az, None, diff=False),
         "kstrong_u8": lambda: ru.kstrong_extract_pc(raw, RES, az),
+        # the same two extractions as fixed-capacity custom ops (padded output + counts, no host read in the call):
+        # the device chain alone, without the ragged-list assembly of the reference-shaped wrappers
+        "cfar_extract_op_u8": lambda: torch.ops.mmb.cfar_extract(raw, az, None, cap_pts, RES, 101, 2.0, 80.0, 5, 1.0, 0.09,
+                                                                 False, 10.0),
+        "kstrong_op_u8": lambda: torch.ops.mmb.kstrong_extract(raw, az, RES, 12, 0.0, 0.216, 2.0, 80.0, -0.31),
         "sample_weights_fwd": lambda: torch.ops.mmb.sample_weights(wmask.detach(), spts, 0.2384),
         "sample_weights_bwd": lambda: torch.autograd.grad(w_keep, wmask, gw, retain_graph=True),
     }

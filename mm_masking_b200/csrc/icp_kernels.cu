@@ -66,6 +66,12 @@ constexpr int GRID_STRIDE = GRID_CELLS + 8;     // ints per pair in the start / 
 #ifndef MMB_ROWS_WARPS
 #define MMB_ROWS_WARPS 8
 #endif
+#ifndef MMB_ROWS_CH
+#define MMB_ROWS_CH 4                            // 32-candidate chunks fetched together in the run walk
+#endif
+#ifndef MMB_ROWS_STATIC
+#define MMB_ROWS_STATIC 0                        // 1: warp w takes slots w, w + 8, ... instead of first come first served
+#endif
 #ifndef MMB_ROWS_INTERLEAVE
 #define MMB_ROWS_INTERLEAVE 0
 #endif
@@ -1412,10 +1418,14 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
 
   // ------------- phase C: the warps take the block's queries one at a time, first come first served -------
   const int nqb = min(GRID_ROWS_QB, a.n - q_first);
-  for (;;) {
+  for (int turn = 0;; ++turn) {
     int slot = 0;
-    if (lane == 0) slot = atomicAdd(&sNext, 1);
-    slot = __shfl_sync(0xffffffffu, slot, 0);
+    if (MMB_ROWS_STATIC) {
+      slot = warp + GRID_ROWS_WARPS * turn;
+    } else {
+      if (lane == 0) slot = atomicAdd(&sNext, 1);
+      slot = __shfl_sync(0xffffffffu, slot, 0);
+    }
     if (slot >= nqb) break;
     const int qi = q_first + slot;
     const double qx = sQ[0][slot], qy = sQ[1][slot], qz = sQ[2][slot];
@@ -1487,9 +1497,9 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
       const float qnan = __int_as_float(0x7fc00000);
       int cs = 0, ce = 0;                                    // what is left of the run being cut (warp-uniform)
       for (;;) {
-        int sa[4], ea[4];
+        int sa[MMB_ROWS_CH], ea[MMB_ROWS_CH];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < MMB_ROWS_CH; ++k) {
           if (cs >= ce && mask) {                            // warp-uniform
             const int c = __ffs(mask) - 1; mask &= mask - 1;
             cs = __shfl_sync(0xffffffffu, s0, c); ce = __shfl_sync(0xffffffffu, e0, c);
@@ -1497,18 +1507,18 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
           sa[k] = cs; cs = min(cs + 32, ce); ea[k] = cs;
         }
         if (sa[0] >= ea[0]) break;                           // nothing left
-        float4 v[4];
+        float4 v[MMB_ROWS_CH];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < MMB_ROWS_CH; ++k) {
           v[k] = make_float4(qnan, 0.f, 0.f, 0.f);           // NaN never passes the filter
           if (sa[k] + lane < ea[k]) v[k] = __ldg(reinterpret_cast<const float4*>(sorted + (sa[k] + lane)));
         }
-        float f[4];
+        float f[MMB_ROWS_CH], fm = __int_as_float(0x7f800000);
 #pragma unroll
-        for (int k = 0; k < 4; ++k) f[k] = filt(v[k]);
-        if (fminf(fminf(f[0], f[1]), fminf(f[2], f[3])) <= thr) {
+        for (int k = 0; k < MMB_ROWS_CH; ++k) { f[k] = filt(v[k]); fm = fminf(fm, f[k]); }
+        if (fm <= thr) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
+          for (int k = 0; k < MMB_ROWS_CH; ++k)
             if (f[k] <= thr) exact_f(v[k]);
         }
       }
