@@ -75,7 +75,10 @@ constexpr int GRID_STRIDE = GRID_CELLS + 8;     // ints per pair in the start / 
 #ifndef MMB_ROWS_INTERLEAVE
 #define MMB_ROWS_INTERLEAVE 0
 #endif
-constexpr int GRID_ROWS_QB_HOST = 4 * MMB_ROWS_WARPS;   // queries per block of icp_rows_kernel (4 per warp)
+#ifndef MMB_ROWS_QB
+#define MMB_ROWS_QB (4 * MMB_ROWS_WARPS > 32 ? 32 : 4 * MMB_ROWS_WARPS)
+#endif
+constexpr int GRID_ROWS_QB_HOST = MMB_ROWS_QB;  // queries per block of icp_rows_kernel
 
 struct IcpPlan {
   int N, n, m, mp, R;            // mp: m rounded up to NN_TILE; R residual rows
@@ -1267,8 +1270,8 @@ constexpr int GRID_ROWS_WARPS = MMB_ROWS_WARPS;
 #ifndef MMB_ROWS_MINBLOCKS
 #define MMB_ROWS_MINBLOCKS 5
 #endif
-constexpr int GRID_ROWS_QB = GRID_ROWS_WARPS * 4;               // queries per block: 8 lanes each in phase A/B, one lane each in the row pass
-static_assert(GRID_ROWS_QB == GRID_ROWS_QB_HOST && GRID_ROWS_QB == GRID_ROWS_WARPS * 4, "block layout");
+constexpr int GRID_ROWS_QB = MMB_ROWS_QB;                       // queries per block: 8 lanes each in phase A/B, one lane each in the row pass
+static_assert(GRID_ROWS_QB == GRID_ROWS_QB_HOST && GRID_ROWS_QB <= GRID_ROWS_WARPS * 4, "block layout");
 constexpr int GRID_ROWS_NVS = 32;                               // doubles per partial slot (NV <= 31)
 static_assert(GRID_ROWS_QB <= 32, "the row pass maps one query to one lane of warp 0");
 
@@ -1377,7 +1380,7 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
   {
     const int g = lane >> 3, r = lane & 7;
     const int slot = warp * 4 + g, qi = q_first + slot;
-    if (qi < a.n) {
+    if (slot < GRID_ROWS_QB && qi < a.n) {                   // with more than QB / 4 warps the extra ones only search
       double qx, qy, qz;
       transform_query<T, DIM>(src + (size_t)qi * 3, sP, qx, qy, qz);
       double D2 = 1.0e308; int I = INT_MAX;
