@@ -49,6 +49,10 @@ WORKLOADS = {
                desc="batched weighted pt2pl ICP, 32 pairs/GPU, 2000 radar pts vs 50000 lidar map pts, 10 it, fwd+bwd"),
     "c5": dict(N=32, n=2000, m=200000, iters=20, dim=3, three_d=True,
                desc="SE(3) pt2pl ICP, 32 pairs/GPU, 2000 pts vs 200000 map pts, 20 it, fwd+bwd"),
+    # the map extends to 2-3x the scan footprint: most targets fall outside the cell grid (which is fitted to the
+    # scan) into the unsorted outside bucket, scanned in full by every query whose bound reaches the grid border
+    "c3wide": dict(N=32, n=2000, m=50000, iters=10, dim=2, three_d=False, scan_range=30.0,
+                   desc="as c3, but the scan covers 30 m of a +-80 m map (map extent ~2.7x the scan footprint)"),
     "small": dict(N=4, n=500, m=5000, iters=5, dim=2, three_d=False, desc="smoke-sized"),
 }
 METRIC = "icp_pairs_per_sec_fwd_bwd"
@@ -129,7 +133,8 @@ def gather_per_rank(value, device):
 
 def make_batch(wl, seed):
     from mm_masking_b200 import synth
-    return synth.make_icp_batch(N=wl["N"], n=wl["n"], m=wl["m"], seed=seed, three_d=wl["three_d"])
+    return synth.make_icp_batch(N=wl["N"], n=wl["n"], m=wl["m"], seed=seed, three_d=wl["three_d"],
+                                scan_range=wl.get("scan_range", 76.0))
 
 
 # ---------------------------------------------------------------------------------------------
@@ -623,7 +628,7 @@ def run_ours(args, wl, rank, world, local_rank):
         #                                    + 4 prior weight + 4 weight history) + m x 16 B + the start table
         per_query = 56 if mode == "rows" else 28
         kname = "icp_rows_kernel" if mode == "rows" else "nn_grid_kernel"
-        grid_bytes = N * (n * per_query + m * 16 + (65536 + 8) * 4)
+        grid_bytes = N * (n * per_query + m * 16 + (65536 + 264) * 4)
         hbm = hbm_peak or 6455.9
         gbs = grid_bytes / (nn_ms * 1e-3) / 1e9
         tr, tr_info = traffic_lookup(kname, args.workload)

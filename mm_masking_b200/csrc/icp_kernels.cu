@@ -62,7 +62,15 @@ constexpr double GRID_MARGIN = 4.0;             // metres added around the scan 
 constexpr double GRID_MARGIN_REL = 0.125;       // ... plus this fraction of its extent, on every side
 constexpr int GRID_OUTSIDE = GRID_CELLS;        // key of the targets that lie outside the grid
 constexpr int GRIDNN_THREADS = 256;
-constexpr int GRID_STRIDE = GRID_CELLS + 8;     // ints per pair in the start / cursor tables (16-byte aligned rows)
+// After the G x G fine cells the tables hold a TAIL: for the Morton backend one outside bucket (entry 0 of the tail),
+// for the row-major backend a coarse 16 x 16 grid over the square of four times the side (same centre; 64 fine
+// cells per coarse cell, row-major) for the targets outside the fine grid, then one far bucket for what lies
+// beyond that (pad rows); entry GRID_TAIL is the end sentinel (= m).
+constexpr int GRID_COARSE = 16;
+constexpr int GRID_TAIL = GRID_COARSE * GRID_COARSE + 1;
+constexpr int GRID_FAR = GRID_CELLS + GRID_COARSE * GRID_COARSE;
+constexpr int GRID_STRIDE = GRID_CELLS + 264;   // ints per pair in the start / cursor tables (16-byte aligned rows; >= GRID_TAIL + 1)
+static_assert(GRID_STRIDE >= GRID_CELLS + GRID_TAIL + 1 && GRID_STRIDE % 4 == 0, "table stride");
 #ifndef MMB_ROWS_WARPS
 #define MMB_ROWS_WARPS 8
 #endif
@@ -638,10 +646,17 @@ __global__ void grid_geom_kernel(const T* __restrict__ source, const double* __r
   }
 }
 
-// row-major key of a point given its cell coordinates (doubles), or GRID_OUTSIDE
+// coarse coordinate (16 cells over [-1.5 G, 2.5 G)) of a fine cell coordinate
+__device__ __forceinline__ double coarse_coord(double f) { return (f + 1.5 * (double)GRID_G) * (4.0 / (double)GRID_G); }
+
+// row-major key of a point given its cell coordinates (doubles): a fine cell, else a coarse cell of the tail, else
+// the far bucket
 __device__ __forceinline__ int grid_key_rows(double fx, double fy) {
-  if (!(fx >= 0.0 && fx < (double)GRID_G && fy >= 0.0 && fy < (double)GRID_G)) return GRID_OUTSIDE;
-  return (int)fy * GRID_G + (int)fx;
+  if (fx >= 0.0 && fx < (double)GRID_G && fy >= 0.0 && fy < (double)GRID_G) return (int)fy * GRID_G + (int)fx;
+  const double cu = coarse_coord(fx), cv = coarse_coord(fy);
+  if (cu >= 0.0 && cu < (double)GRID_COARSE && cv >= 0.0 && cv < (double)GRID_COARSE)
+    return GRID_CELLS + (int)cv * GRID_COARSE + (int)cu;
+  return GRID_FAR;                                            // also NaN / infinite coordinates
 }
 
 // ranks == nullptr: Morton keys (nn_grid_kernel).  ranks != nullptr: row-major keys (icp_rows_kernel) and the
@@ -699,11 +714,25 @@ __global__ void __launch_bounds__(1024) grid_scan_kernel(int* __restrict__ count
     st4[i * 32 + lane] = r; cnt4[i * 32 + lane] = r;
     run += __shfl_sync(0xffffffffu, inc, 31);
   }
-  if (tid == 1023) {
-    int* cnt = counts + (size_t)b * GRID_STRIDE;
-    int* st = start + (size_t)b * GRID_STRIDE;
-    const int outside = cnt[GRID_OUTSIDE];
-    st[GRID_OUTSIDE] = run; cnt[GRID_OUTSIDE] = run; st[GRID_OUTSIDE + 1] = run + outside;
+  // the tail (outside bucket / coarse cells / far bucket): GRID_TAIL entries and the end sentinel, by the last warp
+  if (warp == 31) {
+    constexpr int PER = (GRID_TAIL + 31) / 32;
+    int* cnt = counts + (size_t)b * GRID_STRIDE + GRID_CELLS;
+    int* st = start + (size_t)b * GRID_STRIDE + GRID_CELLS;
+    int c[PER], local = 0;
+#pragma unroll
+    for (int k = 0; k < PER; ++k) { const int t = lane * PER + k; c[k] = t < GRID_TAIL ? cnt[t] : 0; local += c[k]; }
+    int inc = local;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+    int at = run + inc - local;                    // `run` is the number of targets in the fine cells
+#pragma unroll
+    for (int k = 0; k < PER; ++k) {
+      const int t = lane * PER + k;
+      if (t < GRID_TAIL) { st[t] = at; cnt[t] = at; }
+      at += c[k];
+    }
+    if (lane == 31) st[GRID_TAIL] = at;
   }
 }
 
@@ -1559,9 +1588,23 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
       walk(lane == c ? s0 : 0, lane == c ? e0 : 0);
       return true;
     };
-    // the outside bucket is one run, held by lane 0
-    auto scan_outside = [&]() {
-      walk(lane == 0 ? __ldg(start + GRID_OUTSIDE) : 0, lane == 0 ? __ldg(start + GRID_OUTSIDE + 1) : 0);
+    // Targets outside the fine grid: the coarse cells (16 x 16, 64 fine cells each) that the square of half-side
+    // Dc around the query touches -- lane v fetches the run of coarse row v -- and, only when that square leaves the
+    // coarse grid too (or there is no bound: Dc = 1e300), the far bucket.
+    auto scan_outside = [&](double Dc) {
+      const int* sc = start + GRID_CELLS;
+      const double cu = coarse_coord(fx), cv = coarse_coord(fy);
+      const double dcc = Dc * (4.0 / (double)GRID_G) + 1.0e-6;                 // coarse cells, widened
+      const double ulo = cu - dcc, uhi = cu + dcc, vlo = cv - dcc, vhi = cv + dcc;
+      int s0 = 0, e0 = 0;
+      if (lane < GRID_COARSE && (double)lane + 1.0 > vlo && (double)lane <= vhi && uhi >= 0.0 && ulo < (double)GRID_COARSE) {
+        const int x0 = ulo <= 0.0 ? 0 : (ulo >= (double)(GRID_COARSE - 1) ? GRID_COARSE - 1 : (int)ulo);
+        const int x1 = uhi >= (double)(GRID_COARSE - 1) ? GRID_COARSE - 1 : (uhi < 0.0 ? 0 : (int)uhi);
+        s0 = __ldg(sc + lane * GRID_COARSE + x0); e0 = __ldg(sc + lane * GRID_COARSE + x1 + 1);
+      }
+      walk(s0, e0);
+      if (!(ulo >= 0.0 && uhi < (double)GRID_COARSE && vlo >= 0.0 && vhi < (double)GRID_COARSE))
+        walk(lane == 0 ? __ldg(sc + GRID_COARSE * GRID_COARSE) : 0, lane == 0 ? __ldg(sc + GRID_TAIL) : 0);
     };
     auto reduce = [&]() {                                    // lexicographic (D2, I) minimum, left in every lane
       const unsigned long long bits = (unsigned long long)__double_as_longlong(D2);
@@ -1583,7 +1626,7 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
       // the bound the rows were chosen with (warp-uniform; the lanes' own minima have moved on)
       const double Dc = sqrt_upper(sQ[3][slot]) * sG[2] * (1.0 + SLACK) + abs_slack;
       if (yy.y - yy.x >= 32) scan_disc(yy.x + 32, yy.y, __double2float_ru(Dc) + ferr);
-      if (!(fx - Dc >= 0.0 && fx + Dc < (double)GRID_G && fy - Dc >= 0.0 && fy + Dc < (double)GRID_G)) scan_outside();
+      if (!(fx - Dc >= 0.0 && fx + Dc < (double)GRID_G && fy - Dc >= 0.0 && fy + Dc < (double)GRID_G)) scan_outside(Dc);
       reduce();
     } else {
       // no bound yet: squares of 3, 5, 9, 17, ... cells around the query's cell until one holds a target
@@ -1609,12 +1652,12 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
         if (x0 == 0 && y0 == 0 && x1 == GRID_G - 1 && y1 == GRID_G - 1) break;      // the whole grid has been scanned
         rad *= 2;
       }
-      if (!(D2 < 1.0e300)) { scan_outside(); reduce(); done = true; }
+      if (!(D2 < 1.0e300)) { scan_outside(1.0e300); reduce(); done = true; }    // nothing in the fine grid: everything outside
       if (!done) {
         const double Dc = sqrt_upper(D2) * sG[2] * (1.0 + SLACK) + abs_slack;        // cells, inflated
         const float Dcf = __double2float_ru(Dc) + ferr;                              // fp32, widened
         scan_disc(clamp_cell_f(fyf - Dcf), clamp_cell_f(fyf + Dcf), Dcf);
-        if (!(fx - Dc >= 0.0 && fx + Dc < (double)GRID_G && fy - Dc >= 0.0 && fy + Dc < (double)GRID_G)) scan_outside();
+        if (!(fx - Dc >= 0.0 && fx + Dc < (double)GRID_G && fy - Dc >= 0.0 && fy + Dc < (double)GRID_G)) scan_outside(Dc);
         reduce();
       }
     }

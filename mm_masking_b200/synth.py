@@ -141,12 +141,13 @@ def bilinear_weights(mask: np.ndarray, pts: np.ndarray) -> np.ndarray:
 
 def make_icp_batch(N: int, n: int, m: int, seed: int = 0, *, three_d: bool = False,
                    pos: float = 2.0, rot: float = 0.6, real_frac: float = 0.95,
-                   clutter_frac: float = 0.3, weights: str = "mask") -> dict:
+                   clutter_frac: float = 0.3, weights: str = "mask", scan_range: float = 76.0) -> dict:
     """One batch of scan/map pairs.
 
     Returns float32 arrays: source (N,n,3), target (N,m,6), T_init (N,4,4), T_gt (N,4,4),
     weight (N,n). `pos`/`rot` are the half-widths of the initial perturbation
-    (reference training values 2 m / 0.6 rad: `train_icp_weights.py:364-365`).
+    (reference training values 2 m / 0.6 rad: `train_icp_weights.py:364-365`).  `scan_range` is the radius the
+    scan covers; the map always covers +-80 m, so a small value gives a map much larger than the scan footprint.
     """
     rng = np.random.default_rng(seed)
     source = np.zeros((N, n, 3), np.float32)
@@ -161,7 +162,7 @@ def make_icp_batch(N: int, n: int, m: int, seed: int = 0, *, three_d: bool = Fal
         gt = se2_matrix(rng.uniform(-3, 3), rng.uniform(-3, 3), rng.uniform(-0.5, 0.5))
         n_real = int(n * rng.uniform(0.9, 1.0))
         n_clutter = int(clutter_frac * n_real)
-        source[b] = sample_scan(rng, segs, gt, n, n_real - n_clutter, n_clutter, three_d=three_d)
+        source[b] = sample_scan(rng, segs, gt, n, n_real - n_clutter, n_clutter, three_d=three_d, max_range=scan_range)
         pert = se2_matrix(rng.uniform(-pos, pos), rng.uniform(-pos, pos), rng.uniform(-rot, rot))
         T_gt[b] = gt
         T_init[b] = pert @ gt

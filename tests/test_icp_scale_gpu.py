@@ -111,3 +111,12 @@ def test_early_exit_and_freezing_at_scale():
     from mm_masking_b200 import synth
     _check(synth.make_icp_batch(N=3, n=2000, m=50000, seed=4, pos=0.5, rot=0.1), dim=2, iters=40,
            const_iter=False, tol=2e-3)
+
+
+def test_map_much_larger_than_the_scan_footprint():
+    """the cell grid is fitted to the scan footprint; with a map 2-3x as large most targets sit in the
+    outside bucket and the queries near the border (or far from everything) scan it.  Exactness must not depend on
+    where a target was binned; `const_iter: False`, so pairs also freeze at different iterations."""
+    from mm_masking_b200 import synth, _capi
+    batch = synth.make_icp_batch(N=3, n=2000, m=50000, seed=6, pos=1.0, rot=0.2, scan_range=30.0)
+    _check(batch, dim=2, iters=25, const_iter=False, tol=2e-3, backends=(_capi.NN_ROWS, _capi.NN_GRID))
