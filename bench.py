@@ -485,14 +485,17 @@ def run_ours(args, wl, rank, world, local_rank):
     launches1 = lib.mmb_launch_count()
     # >= 3 repeats of the K-step loop, median reported (20 steps are ~25 ms: too short for one sample of a
     # loop whose uploads overlap the kernels)
-    e2e_ms = []
+    e2e_ms, e2e_host_ms = [], []
     for rep in range(max(1, args.e2e_repeats)):
         ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        h0 = time.perf_counter()
         ea.record()
         for _ in range(args.steps):
             flush.fill_(1)
             step_e2e(next(pre))
         eb.record()
+        e2e_host_ms.append(1e3 * (time.perf_counter() - h0) / args.steps)     # host time to ISSUE a step (no sync)
         barrier()
         e2e_rank = gather_per_rank(ea.elapsed_time(eb) / args.steps, dev)
         e2e_ms.append(max(e2e_rank))
@@ -664,7 +667,7 @@ def run_ours(args, wl, rank, world, local_rank):
         "e2e": {"value": world * N / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": h2d_per_step, "d2h_bytes_per_step": d2h,
                 "serial_upload_value": world * N / (ms_e2e_serial * 1e-3),
-                "repeats_ms_per_step": e2e_ms,
+                "repeats_ms_per_step": e2e_ms, "host_issue_ms_per_step": e2e_host_ms,
                 "overlap": "H2D of step k+1 on a copy stream under the kernels of step k (DevicePrefetcher); "
                            "K uploads inside the timed region, L2 flush time included"},
         # kernels of this library launched inside the two timed regions behind `value` and `e2e`, COUNTED by the
