@@ -93,30 +93,80 @@ def traffic_lookup(kernel, workload):
     return best.get("dram_bytes_per_launch"), {"traffic_stale": False, "traffic_source": best.get("capture"), "source_sha": sha}
 
 
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if "-" in part:
+            a, b = part.split("-"); cpus.update(range(int(a), int(b) + 1))
+        elif part:
+            cpus.add(int(part))
+    return cpus
+
+
 def bind_to_gpu_numa_node(local_rank):
-    """Pin this rank to the CPU cores local to its GPU BEFORE any pinned host memory is allocated, so that the
-    pinned staging buffers are first-touched on the GPU's NUMA node and 8 ranks do not all upload through one
-    socket (the r01 end-to-end scaling loss).  Reads the PCI topology from sysfs; a no-op when it is not exposed."""
+    """Run this rank on CPU cores local to its GPU WHILE its pinned host buffers are allocated (first touch places
+    them on that NUMA node), so that 8 ranks do not all upload through one socket -- the r01 end-to-end scaling
+    loss; at N = 8 the four ranks whose buffers sat on the remote socket uploaded at 21 GB/s against 33 GB/s.
+    The PCI topology comes from sysfs; where the container hides it (the GPU-local list covers every allowed core)
+    the node is found empirically: the allowed cores are split into four contiguous groups, a pinned 64 MB buffer is
+    allocated and first-touched from each, and the group whose buffer uploads fastest wins.  Returns a dict for the
+    JSON line; call `restore_affinity` after the allocations."""
+    import torch
+    allowed = set(os.sched_getaffinity(0))
+    info = {"bound": False, "allowed_cpus": len(allowed)}
     try:
-        import torch
-        bus = torch.cuda.get_device_properties(local_rank).pci_bus_id
-        dom = torch.cuda.get_device_properties(local_rank).pci_domain_id
-        dev = torch.cuda.get_device_properties(local_rank).pci_device_id
-        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/local_cpulist"
-        cpus = set()
-        for part in open(path).read().strip().split(","):
-            if "-" in part:
-                a, b = part.split("-"); cpus.update(range(int(a), int(b) + 1))
-            elif part:
-                cpus.add(int(part))
-        allowed = os.sched_getaffinity(0)
-        cpus &= allowed
+        pr = torch.cuda.get_device_properties(local_rank)
+        path = f"/sys/bus/pci/devices/{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0/local_cpulist"
+        cpus = _parse_cpulist(open(path).read()) & allowed
         if cpus and cpus != allowed:
             os.sched_setaffinity(0, cpus)
-            return {"bound": True, "cpus": len(cpus), "numa_node": open(path.replace("local_cpulist", "numa_node")).read().strip()}
-        return {"bound": False, "cpus": len(allowed), "why": "GPU-local CPU list covers the whole allowance"}
+            info.update(bound=True, how="sysfs local_cpulist", cpus=len(cpus))
+            return info
     except Exception as e:                       # containers often hide sysfs topology
-        return {"bound": False, "why": type(e).__name__}
+        info["sysfs"] = type(e).__name__
+    if len(allowed) < 8:
+        info["why"] = "fewer than 8 cores allowed: nothing to choose between"
+        return info
+    try:
+        order = sorted(allowed)
+        groups = [set(order[i * len(order) // 4:(i + 1) * len(order) // 4]) for i in range(4)]
+        dev = torch.device("cuda", local_rank)
+        dst = torch.empty(64 << 20, dtype=torch.uint8, device=dev)
+        rates = []
+        for g in groups:
+            os.sched_setaffinity(0, g)
+            buf = torch.empty(64 << 20, dtype=torch.uint8).pin_memory()      # allocated and first-touched from group g
+            dst.copy_(buf, non_blocking=True); torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(4):
+                dst.copy_(buf, non_blocking=True)
+            b.record(); torch.cuda.synchronize()
+            rates.append(4 * buf.numel() / (a.elapsed_time(b) * 1e-3) / 1e9)
+            del buf
+            if hasattr(torch._C, "_host_emptyCache"):
+                torch._C._host_emptyCache()          # the probe block must not be recycled for the real buffers
+        best = max(range(4), key=lambda i: rates[i])
+        info["probe_gbs"] = [round(r, 1) for r in rates]
+        if rates[best] > 1.15 * min(rates):
+            os.sched_setaffinity(0, groups[best])
+            info.update(bound=True, how="empirical: fastest of four core groups for a pinned upload", cpus=len(groups[best]),
+                        group=best)
+        else:
+            os.sched_setaffinity(0, allowed)
+            info["why"] = "all core groups upload at the same rate"
+        del dst
+    except Exception as e:
+        os.sched_setaffinity(0, allowed)
+        info["probe_error"] = f"{type(e).__name__}: {e}"
+    return info
+
+
+def restore_affinity(allowed):
+    try:
+        os.sched_setaffinity(0, allowed)
+    except Exception:
+        pass
 
 
 def gather_per_rank(value, device):
@@ -407,6 +457,7 @@ def run_ours(args, wl, rank, world, local_rank):
     lib = _capi.load_library()
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    cpus_allowed = set(os.sched_getaffinity(0))
     numa = bind_to_gpu_numa_node(local_rank)      # before pin_memory()
     if world > 1:
         import datetime
@@ -419,6 +470,7 @@ def run_ours(args, wl, rank, world, local_rank):
     d_w = host["weight"].to(dev).requires_grad_(True)
     out_T = torch.empty((N, 4, 4), dtype=torch.float32).pin_memory()
     out_gw = torch.empty((N, n), dtype=torch.float32).pin_memory()
+    restore_affinity(cpus_allowed)                # the buffers stay where they were first touched
 
     alg = ICP(icp_type="pt2pl", differentiable=True, max_iterations=K, tolerance=1e-5)
     alg.const_iter = True
