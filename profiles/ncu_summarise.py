@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--queries", type=float, default=0, help="divide instruction counts by this (e.g. queries per launch)")
     ap.add_argument("--top", type=int, default=30)
     ap.add_argument("--kernel", default="", help="substring of the kernel name whose source lines are listed (default: the first)")
+    ap.add_argument("--instance", type=int, default=0, help="which launch of that kernel (0 = the first captured)")
     args = ap.parse_args()
     rows = list(csv.reader(io.StringIO(ncu(["-i", args.report, "--page", "raw", "--csv"]))))
     hdr, units = rows[0], rows[1]
@@ -44,11 +45,19 @@ def main():
     total_inst = total_samp = 0
     col = None
     active = False
+    seen = -1
+    cur_file = ""
     for r in src:
+        if len(r) >= 2 and r[0] in ("File Path", "File Name"):
+            cur_file = r[1]
+            continue
         if len(r) >= 2 and r[0] == "Function Name":
             if active:
                 break
-            active = args.kernel in r[1]
+            main = cur_file.endswith("_kernels.cu")          # the export has one block per (launch, source file)
+            if args.kernel in r[1] and main:
+                seen += 1
+            active = args.kernel in r[1] and main and seen == args.instance
             col = None
             continue
         if not active:
