@@ -153,20 +153,28 @@ def bind_to_gpu_numa_node(local_rank):
             info.update(bound=True, how="empirical: fastest of four core groups for a pinned upload", cpus=len(groups[best]),
                         group=best)
         else:
-            os.sched_setaffinity(0, allowed)
+            restore_affinity(allowed)
             info["why"] = "all core groups upload at the same rate"
         del dst
     except Exception as e:
-        os.sched_setaffinity(0, allowed)
+        restore_affinity(allowed)
         info["probe_error"] = f"{type(e).__name__}: {e}"
     return info
 
 
 def restore_affinity(allowed):
+    """give EVERY thread of the process its full CPU allowance back: worker threads (the torch intra-op pool) that
+    were created while the main thread was bound inherit the narrow mask and would keep it -- the CPU baseline of
+    this very run would then be timed on a quarter of the cores"""
     try:
-        os.sched_setaffinity(0, allowed)
+        tids = [int(t) for t in os.listdir("/proc/self/task")]
     except Exception:
-        pass
+        tids = [0]
+    for tid in tids + [0]:
+        try:
+            os.sched_setaffinity(tid, allowed)
+        except Exception:
+            pass
 
 
 def gather_per_rank(value, device):

@@ -8,11 +8,6 @@ the map points alone are 38 MB per batch - about as long on PCIe as the whole IC
 `DevicePrefetcher` wraps the same iterator and hands out device copies: the upload of batch k+1 is
 enqueued on a dedicated copy stream before batch k is returned, so it runs under the kernels of batch
 k.  Every batch is still copied exactly once per step; nothing is cached across steps.
-
-Large pinned tensors are uploaded in two halves on two copy streams: on the pool's B200 boxes (PCIe 5 x16) one
-`cudaMemcpyAsync` stream sustains 31 GB/s, two sustain 47 GB/s (`profiles/h2d_probe.py`), which is the difference
-between an upload that is longer than the c3 step (39.4 MB: 1.0 ms against 0.86 ms of kernels) and one that hides
-under it (0.83 ms).
 """
 from __future__ import annotations
 
@@ -55,52 +50,14 @@ class DevicePrefetcher:
     be pinned (`pin_batch`), otherwise the copy blocks the host.  With a CPU device it is a plain
     pass-through (host-side tests)."""
 
-    SPLIT_BYTES = 4 << 20          # pinned tensors at least this large go up in two halves on two copy streams
-
     def __init__(self, iterable, device):
         self.device = torch.device(device)
         self._it = iter(iterable)
         self._cuda = self.device.type == "cuda"
         self._stream = torch.cuda.Stream(self.device) if self._cuda else None
-        self._stream2 = torch.cuda.Stream(self.device) if self._cuda else None
         self._next = None
         self.bytes_uploaded = 0
         self._preload()
-
-    def _upload(self, host):
-        """device copy of a nested host batch; returns (device batch, events the consumer waits on)"""
-        second = []                                      # (dst half, src half) for the second copy stream
-
-        def up(t):
-            if t.is_cuda:
-                return t.to(self.device, non_blocking=True)
-            nbytes = t.numel() * t.element_size()
-            if nbytes >= self.SPLIT_BYTES and t.is_pinned() and t.is_contiguous():
-                dst = torch.empty(t.shape, dtype=t.dtype, device=self.device)
-                half = t.numel() // 2
-                second.append((dst, dst.view(-1)[half:], t.view(-1)[half:], t.view(-1)[:half]))
-                return dst
-            return t.to(self.device, non_blocking=True)
-
-        with torch.cuda.stream(self._stream):
-            dev = _map_tensors(host, up)
-            ready = torch.cuda.Event()
-            ready.record(self._stream)                   # allocations (and the small copies) are ordered before stream 2
-            for dst, _, _, src_lo in second:
-                dst.view(-1)[:src_lo.numel()].copy_(src_lo, non_blocking=True)
-            ev = torch.cuda.Event()
-            ev.record(self._stream)
-        events = [ev]
-        if second:
-            self._stream2.wait_event(ready)
-            with torch.cuda.stream(self._stream2):
-                for dst, dst_hi, src_hi, _ in second:
-                    dst_hi.copy_(src_hi, non_blocking=True)
-                    dst.record_stream(self._stream2)
-                ev2 = torch.cuda.Event()
-                ev2.record(self._stream2)
-            events.append(ev2)
-        return dev, events
 
     def _preload(self):
         try:
@@ -111,9 +68,12 @@ class DevicePrefetcher:
         if not self._cuda:
             self._next = (_map_tensors(host, lambda t: t.to(self.device)), None)
             return
-        dev, events = self._upload(host)
+        with torch.cuda.stream(self._stream):
+            dev = _map_tensors(host, lambda t: t.to(self.device, non_blocking=True))
+            ev = torch.cuda.Event()
+            ev.record(self._stream)
         self.bytes_uploaded += sum(t.numel() * t.element_size() for t in _tensors(host, []) if not t.is_cuda)
-        self._next = (dev, events)
+        self._next = (dev, ev)
 
     def __iter__(self):
         return self
@@ -124,8 +84,7 @@ class DevicePrefetcher:
         dev, ev = self._next
         if self._cuda:
             cur = torch.cuda.current_stream(self.device)
-            for e in ev:
-                cur.wait_event(e)
+            cur.wait_event(ev)
             for t in _tensors(dev, []):
                 t.record_stream(cur)
         self._preload()

@@ -45,20 +45,3 @@ def test_prefetcher_uploads_each_batch_once_and_in_order():
         junk.fill_(k)
         assert torch.equal((b["list"][0] * 2).cpu(), host[k]["list"][0] * 2)
     assert pre.bytes_uploaded == 3 * per
-
-
-@pytest.mark.gpu
-def test_large_pinned_tensors_go_up_in_two_halves_and_arrive_intact():
-    """tensors of at least SPLIT_BYTES are uploaded in two halves on two copy streams (47 vs 31 GB/s on the pool's
-    boxes); the consumer must see complete data whatever the interleaving with its own kernels"""
-    g = torch.Generator().manual_seed(0)
-    host = [pin_batch({"map": torch.rand((3, 700001, 2), generator=g), "odd": torch.rand(1048577 * 2 + 1, generator=g),
-                       "small": torch.rand(7, generator=g)}) for _ in range(4)]
-    assert host[0]["map"].numel() * 4 >= DevicePrefetcher.SPLIT_BYTES
-    pre = DevicePrefetcher(iter(host), "cuda:0")
-    junk = torch.empty(128 << 20, dtype=torch.uint8, device="cuda:0")
-    for k, b in enumerate(pre):
-        junk.fill_(k)
-        for name in ("map", "odd", "small"):
-            assert torch.equal(b[name].cpu(), host[k][name]), name
-    assert pre.bytes_uploaded == 4 * sum(t.numel() * 4 for t in host[0].values())
