@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define MMB_ABI_VERSION 4
+#define MMB_ABI_VERSION 5
 
 typedef enum mmb_status {
   MMB_OK = 0,
@@ -30,7 +30,8 @@ typedef enum mmb_status {
   MMB_ERR_UNSUPPORTED = 3,
   MMB_ERR_WORKSPACE_TOO_SMALL = 4,
   MMB_ERR_MISALIGNED = 5,
-  MMB_ERR_CUDA = 6
+  MMB_ERR_CUDA = 6,
+  MMB_ERR_SCRATCH_LIMIT = 7   /* mmb_nn_search_static: the problem needs more than MMB_NN_STATIC_SCRATCH_BYTES */
 } mmb_status;
 
 enum { MMB_F32 = 0, MMB_F64 = 1 };
@@ -141,6 +142,23 @@ int mmb_nn_search(int32_t N, int32_t n, int32_t m, int32_t target_cols, int32_t 
                   int32_t dim, int32_t nn_slices, int32_t nn_backend, const void* query,
                   const void* target, int32_t* idx_out, void* workspace, size_t workspace_bytes,
                   void* stream);
+
+/* The same search for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Arguments, results and error codes are those of mmb_nn_search without the workspace: the scratch memory is a
+ * file-scope `static __device__` array of MMB_NN_STATIC_SCRATCH_BYTES inside the library (every GPU that loads the
+ * library holds that much until the process exits).  The call allocates nothing (no cudaMalloc / cudaFree, no
+ * allocating library routine) and launches the same kernels, so idx_out is bit-identical to mmb_nn_search's.
+ *   - a problem whose mmb_nn_workspace_bytes(...) exceeds MMB_NN_STATIC_SCRATCH_BYTES is rejected with
+ *     MMB_ERR_SCRATCH_LIMIT before anything is launched (16 MiB holds e.g. 4 x (2 000 queries, 50 000 targets) fp32);
+ *   - every call on a device shares the one array and finds the previous call's contents in it; the call clears
+ *     what must start at zero itself, on `stream`.  Calls that overlap on the GPU (two streams, two host threads,
+ *     two graphs replayed concurrently) RACE on the array: serialise them, or use mmb_nn_search with one workspace
+ *     per stream. */
+#define MMB_NN_STATIC_SCRATCH_BYTES (16u << 20)
+int mmb_nn_search_static(int32_t N, int32_t n, int32_t m, int32_t target_cols, int32_t dtype,
+                         int32_t dim, int32_t nn_slices, int32_t nn_backend, const void* query,
+                         const void* target, int32_t* idx_out, void* stream);
 
 
 /* ------------------------------------------------------------------------------------------

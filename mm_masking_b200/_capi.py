@@ -68,6 +68,7 @@ SIGNATURES = {
     "mmb_icp_backward": (C.c_int, [C.POINTER(IcpParams)] + [_P] * 11 + [C.c_size_t, _P]),
     "mmb_nn_workspace_bytes": (C.c_size_t, [C.c_int32] * 6),
     "mmb_nn_search": (C.c_int, [C.c_int32] * 8 + [_P] * 4 + [C.c_size_t, _P]),
+    "mmb_nn_search_static": (C.c_int, [C.c_int32] * 8 + [_P] * 4),
     "mmb_sample_weights_fwd": (C.c_int, [C.c_int32] * 6 + [C.c_double, _P, _P, _P, _P]),
     "mmb_sample_weights_bwd": (C.c_int, [C.c_int32] * 6 + [C.c_double, _P, _P, _P, _P]),
     "mmb_sample_weights_bwd_det_workspace_bytes": (C.c_size_t, [C.c_int32] * 5),
@@ -110,7 +111,7 @@ def load_library(path: str | None = None):
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)
         fn.restype, fn.argtypes = res, args
-    if lib.mmb_abi_version() != 4:
+    if lib.mmb_abi_version() != 5:
         raise MmbError("libmm_masking_b200.so ABI version mismatch")
     _lib = lib
     return lib

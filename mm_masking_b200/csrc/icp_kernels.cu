@@ -2529,6 +2529,33 @@ static int run_nn_search(const IcpPlan& pl, int cols, int dim, const void* query
   return check_launch();
 }
 
+// ---------------------------------------------------------------------------------------------
+// mmb_nn_search_static: the scratch memory of the search as a file-scope device array (no allocation)
+// ---------------------------------------------------------------------------------------------
+// One array per GPU that loads the library, held until the process exits.  In host code the NAME is a host-side
+// stand-in, not a device address: the kernels are given what cudaGetSymbolAddress returns for the current device,
+// looked up once per device.
+static __device__ __align__(256) unsigned char g_nn_static_scratch[MMB_NN_STATIC_SCRATCH_BYTES];
+
+constexpr int NN_STATIC_MAX_DEVICES = 64;
+static std::atomic<void*> g_nn_static_ptr[NN_STATIC_MAX_DEVICES];
+
+// device address of the array on the CURRENT device (set-up: once per device; afterwards one atomic load)
+static int nn_static_scratch(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { set_last_cuda_error(e); return MMB_ERR_CUDA; }
+  if (dev < 0 || dev >= NN_STATIC_MAX_DEVICES) return MMB_ERR_UNSUPPORTED;
+  void* ptr = g_nn_static_ptr[dev].load(std::memory_order_acquire);
+  if (!ptr) {
+    e = cudaGetSymbolAddress(&ptr, g_nn_static_scratch);
+    if (e != cudaSuccess || !ptr) { set_last_cuda_error(e); return MMB_ERR_CUDA; }
+    g_nn_static_ptr[dev].store(ptr, std::memory_order_release);     // two racing threads store the same address
+  }
+  *out = ptr;
+  return MMB_OK;
+}
+
 }  // namespace mmb
 
 using namespace mmb;
@@ -2546,6 +2573,7 @@ const char* mmb_status_string(int status) {
     case MMB_ERR_WORKSPACE_TOO_SMALL: return "workspace too small";
     case MMB_ERR_MISALIGNED: return "pointer not 16-byte aligned";
     case MMB_ERR_CUDA: return "CUDA error";
+    case MMB_ERR_SCRATCH_LIMIT: return "the problem needs more scratch memory than the static device array holds (MMB_NN_STATIC_SCRATCH_BYTES)";
     default: return "unknown status";
   }
 }
@@ -2649,6 +2677,30 @@ int mmb_nn_search(int32_t N, int32_t n, int32_t m, int32_t target_cols, int32_t 
   const IcpPlan pl = make_plan(N, n, m, MMB_PT2PL, 3, nn_slices, nn_backend, dtype);
   IcpWorkspace w = carve_workspace(workspace, pl);
   if (workspace_bytes < w.bytes) return MMB_ERR_WORKSPACE_TOO_SMALL;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == MMB_F32)
+    return dim == 2 ? run_nn_search<float, 2>(pl, target_cols, dim, query, target, idx_out, w, st)
+                    : run_nn_search<float, 3>(pl, target_cols, dim, query, target, idx_out, w, st);
+  return dim == 2 ? run_nn_search<double, 2>(pl, target_cols, dim, query, target, idx_out, w, st)
+                  : run_nn_search<double, 3>(pl, target_cols, dim, query, target, idx_out, w, st);
+}
+
+int mmb_nn_search_static(int32_t N, int32_t n, int32_t m, int32_t target_cols, int32_t dtype, int32_t dim,
+                         int32_t nn_slices, int32_t nn_backend, const void* query, const void* target, int32_t* idx_out,
+                         void* stream) {
+  if (N <= 0 || n <= 0 || m <= 0 || (target_cols != 3 && target_cols != 6)) return MMB_ERR_INVALID_SHAPE;
+  if (dtype != MMB_F32 && dtype != MMB_F64) return MMB_ERR_UNSUPPORTED;
+  if (dim != 2 && dim != 3) return MMB_ERR_UNSUPPORTED;
+  if (nn_backend < MMB_NN_AUTO || nn_backend > MMB_NN_ROWS) return MMB_ERR_UNSUPPORTED;
+  if (!query || !target || !idx_out) return MMB_ERR_NULL_POINTER;
+  const IcpPlan pl = make_plan(N, n, m, MMB_PT2PL, 3, nn_slices, nn_backend, dtype);
+  if (carve_workspace(nullptr, pl).bytes > (size_t)MMB_NN_STATIC_SCRATCH_BYTES) return MMB_ERR_SCRATCH_LIMIT;
+  void* scratch = nullptr;
+  const int rc = nn_static_scratch(&scratch);
+  if (rc) return rc;
+  // the array keeps the previous call's contents: the search itself clears what must start at zero (the cell
+  // counters, build_grid) and overwrites the rest before reading it, exactly as with a caller's workspace
+  const IcpWorkspace w = carve_workspace(scratch, pl);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (dtype == MMB_F32)
     return dim == 2 ? run_nn_search<float, 2>(pl, target_cols, dim, query, target, idx_out, w, st)

@@ -47,7 +47,7 @@ def test_every_declared_symbol_is_exported_and_bound(lib):
 
 
 def test_status_strings(lib):
-    assert lib.mmb_abi_version() == 4
+    assert lib.mmb_abi_version() == 5
     assert lib.mmb_status_string(0) == b"ok"
     assert lib.mmb_status_string(4) == b"workspace too small"
     assert lib.mmb_status_string(99) == b"unknown status"
