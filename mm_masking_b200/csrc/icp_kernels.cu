@@ -80,6 +80,9 @@ static_assert(GRID_STRIDE >= GRID_CELLS + GRID_TAIL + 1 && GRID_STRIDE % 4 == 0,
 #ifndef MMB_ROWS_STATIC
 #define MMB_ROWS_STATIC 0                        // 1: warp w takes slots w, w + 8, ... instead of first come first served
 #endif
+#ifndef MMB_ROWS_PERSIST
+#define MMB_ROWS_PERSIST 1                       // 1: one launch runs all iterations (work queue + per-pair ready flags)
+#endif
 #ifndef MMB_ROWS_INTERLEAVE
 #define MMB_ROWS_INTERLEAVE 0
 #endif
@@ -159,7 +162,8 @@ struct IcpWorkspace {
   int* conv;                     // (N)
   int* n_matched;                // (N) rows with w > thresh in the latest iteration
   int* n_start;                  // (N) rows with prior weight > thresh
-  int* counters;                 // [0] pairs frozen, [1] 0 or (iteration in which the last pair froze) + 1, [2] iterations executed
+  int* counters;                 // [0] pairs frozen, [1] 0 or (iteration in which the last pair froze) + 1, [2] iterations executed,
+                                 // [3] latest (iteration in which a pair froze) + 1, [4] work queue of the persistent launch
   int* allzero;                  // (N) this iteration's weights of the pair are all zero (ICP.py:215-218)
   // cell-grid backend
   double* geom;                  // (N,4) origin x, y, 1/cell, cell
@@ -170,7 +174,8 @@ struct IcpWorkspace {
   // row-major backend only
   int* ranks;                    // (N,m) arrival rank of every target within its cell (counting pass) -> scatter without atomics
   double* partials;              // (N, nblk, 32) per-block partial sums of the normal equations
-  int* arrive;                   // (N) blocks of the pair that have parked their partials in this launch
+  int* arrive;                   // (N) blocks of the pair that have parked their partials in this iteration
+  int* ready;                    // (N) persistent launch: iterations of the pair that are complete (INT_MAX once it froze)
   size_t bytes;
 };
 
@@ -204,6 +209,8 @@ static IcpWorkspace carve_workspace(void* base, const IcpPlan& pl) {
   w.ranks = c.take<int>(pl.grid == 2 ? Nm : 0);
   w.partials = c.take<double>(pl.grid == 2 ? (size_t)pl.N * pl.nblk * 32 : 0);
   w.arrive = c.take<int>(pl.grid == 2 ? pl.N : 0);
+  w.ready = c.take<int>(pl.grid == 2 ? pl.N : 0);
+  if (pl.grid != 2) { w.arrive = nullptr; w.ready = nullptr; }   // take(0) is the END of the workspace, not "absent"
   w.bytes = c.off;
   return w;
 }
@@ -239,7 +246,7 @@ static IcpSaved carve_saved(void* base, const IcpPlan& pl, int K) {
 template <typename T>
 __global__ void init_state_kernel(const T* __restrict__ T_init, IcpWorkspace w, int N) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b == 0) { w.counters[0] = 0; w.counters[1] = 0; w.counters[2] = 0; }
+  if (b == 0) { w.counters[0] = 0; w.counters[1] = 0; w.counters[2] = 0; w.counters[3] = 0; w.counters[4] = 0; }
   if (b >= N) return;
   const T* Ti = T_init + (size_t)b * 16;
   double* P = w.pose + (size_t)b * 12;
@@ -249,7 +256,7 @@ __global__ void init_state_kernel(const T* __restrict__ T_init, IcpWorkspace w, 
   }
   w.prev_cost[b] = 0.0; w.num_iters[b] = 0.0; w.match_ratio[b] = 0.0;
   w.frozen[b] = 0; w.conv[b] = 0; w.n_matched[b] = 0; w.n_start[b] = 0;
-  if (w.arrive) w.arrive[b] = 0;
+  if (w.arrive) { w.arrive[b] = 0; w.ready[b] = 0; }
 }
 
 __global__ void identity_pose_kernel(double* pose, int N) {
@@ -1322,25 +1329,74 @@ __device__ __forceinline__ float sqrt_upper_ff(float v) {
   return r * 1.00000048f;
 }
 
-template <typename T, int ICP, int DIM, bool FUSED>
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// PERSIST: ONE launch runs every iteration of every pair.  The resident blocks take work items (iteration, pair,
+// 32-query group) off a queue in iteration-major order; an item of iteration k waits until the pair's iteration
+// k - 1 is complete (`ready[pair]`, released by the block that solved it) -- not until EVERY pair is, which is what
+// a launch boundary per iteration costs: the tail of each iteration (the SMs drain while the last blocks finish)
+// and the launch ramp disappear, and a pair far from convergence no longer holds up the others.  Every item
+// depends only on items handed out before it, and an item is only taken by a block that is already running, so
+// the item with the smallest number among the unfinished ones can always proceed: no co-residency assumption.
+template <typename T, int ICP, int DIM, bool FUSED, bool PERSIST>
 __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_rows_kernel(RowsArgs a) {
   constexpr int D = Dof<DIM>::D;
   constexpr int NA = D * (D + 1) / 2;
   constexpr int NV = NA + D + 4;
   constexpr int ROWS = ICP == MMB_PT2PT ? 3 : 1;
+  static_assert(FUSED || !PERSIST, "the search-only form is one launch per call");
   pdl_wait();
   pdl_trigger();
-  // consecutive blocks cycle through the pairs, so that at any moment (and in the tail of the launch) the
-  // resident blocks are a mix of cheap (converged) and expensive (far from the map) pairs
-  const int b = MMB_ROWS_INTERLEAVE ? (int)(blockIdx.x % (unsigned)a.N) : (int)blockIdx.y;
-  const int blk = MMB_ROWS_INTERLEAVE ? (int)(blockIdx.x / (unsigned)a.N) : (int)blockIdx.x;
-  const int it = a.it;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (FUSED && a.w.counters[1] && it >= a.w.counters[1]) return;   // every pair converged in an earlier iteration
   const int R = a.n * ROWS;
+  __shared__ int sItem;
+#define ROWS_NEXT { if (PERSIST) continue; else return; }
+  for (;;) {
+  int it, b, blk;
+  if (PERSIST) {
+    // warp 1 takes the block's next item (and waits for the pair) while warp 0 may still be in the row pass of
+    // the previous one; the barrier below is also what frees the previous item's shared state
+    if (tid == 32) {
+      const int per = a.N * a.nblk;
+      int item = atomicAdd(&a.w.counters[4], 1);
+      if (item < a.K * per) {
+        const int it_ = item / per, b_ = (item - it_ * per) / a.nblk;
+        const int stop = *reinterpret_cast<volatile int*>(a.w.counters + 1);
+        if (stop && it_ >= stop) item = -1;                  // every pair converged in an earlier iteration
+        else while (ld_acquire_gpu(a.w.ready + b_) < it_) __nanosleep(32);
+      } else {
+        item = -1;
+      }
+      sItem = item;
+    }
+    __syncthreads();
+    const int item = sItem;
+    if (item < 0) return;
+    const int per = a.N * a.nblk;
+    it = item / per; b = (item - it * per) / a.nblk; blk = item - it * per - b * a.nblk;
+    if (*reinterpret_cast<volatile int*>(a.w.frozen + b)) {   // converged: icp_finish_kernel repeats its histories
+      __syncthreads();                                        // sItem has been read by every warp
+      continue;
+    }
+  } else {
+    // consecutive blocks cycle through the pairs, so that at any moment (and in the tail of the launch) the
+    // resident blocks are a mix of cheap (converged) and expensive (far from the map) pairs
+    b = MMB_ROWS_INTERLEAVE ? (int)(blockIdx.x % (unsigned)a.N) : (int)blockIdx.y;
+    blk = MMB_ROWS_INTERLEAVE ? (int)(blockIdx.x / (unsigned)a.N) : (int)blockIdx.x;
+    it = a.it;
+    if (FUSED && a.w.counters[1] && it >= a.w.counters[1]) return;   // every pair converged in an earlier iteration
+  }
+  const int warm = PERSIST ? (it > 0 ? 1 : 0) : a.warm;
   const int q_first = blk * GRID_ROWS_QB;
 
-  if (FUSED && a.w.frozen[b]) {
+  if (FUSED && !PERSIST && a.w.frozen[b]) {
     // prior weights are zero (ICP.py:246-247): the step is 0 and the histories repeat (ICP.py:215-224)
     T* wh = static_cast<T*>(a.weights_hist) + ((size_t)b * a.K + it) * R;
     for (int i = q_first * ROWS + tid; i < min((q_first + GRID_ROWS_QB) * ROWS, R); i += blockDim.x)
@@ -1413,7 +1469,7 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
       double qx, qy, qz;
       transform_query<T, DIM>(src + (size_t)qi * 3, sP, qx, qy, qz);
       double D2 = 1.0e308; int I = INT_MAX;
-      if (a.warm) {
+      if (warm) {
         const int j0 = a.w.idx_cur[(size_t)b * a.n + qi];
         if (j0 >= 0 && j0 < a.m) {
           const double d0 = exact_dist2<T, DIM>(tgt + (size_t)j0 * a.cols, qx, qy, qz);
@@ -1672,7 +1728,7 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
   }
   if (!FUSED) return;
   __syncthreads();
-  if (warp != 0) return;
+  if (warp != 0) ROWS_NEXT
 
   // ------------------------- residual rows of the block's queries: one per lane -----------------
   const int i = q_first + lane;
@@ -1748,7 +1804,7 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
   int ticket = 0;
   if (lane == 0) ticket = atomicAdd(a.w.arrive + b, 1);
   ticket = __shfl_sync(0xffffffffu, ticket, 0);
-  if (ticket != a.nblk - 1) return;
+  if (ticket != a.nblk - 1) ROWS_NEXT
 
   // ------------------------- last block of the pair: solve and pose update ----------------------
   __threadfence();
@@ -1770,9 +1826,9 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     sTot[lane] = s;
   }
   __syncwarp();
-  int allzero = 0;
+  int allzero = 0, ready_next = it + 1;
   if (lane == 0) {
-    a.w.arrive[b] = 0;                                       // re-armed for the next iteration's launch
+    a.w.arrive[b] = 0;                                       // re-armed for the next iteration
     const double* tot = sTot;
     T* dl = static_cast<T*>(a.deltas) + ((size_t)b * a.K + it) * 6;
     T* cs = static_cast<T*>(a.costs) + (size_t)b * a.K + it;
@@ -1823,30 +1879,70 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
         if (a.w.num_iters[b] == 0.0) a.w.num_iters[b] = (double)(it + 1);
         if (a.w.match_ratio[b] == 0.0) a.w.match_ratio[b] = (double)matched / (double)(at_start > 0 ? at_start : 1);
         a.w.frozen[b] = 1;
-        const int nf = atomicAdd(&a.w.counters[0], 1) + 1;
-        if (nf == a.N) a.w.counters[1] = it + 1;                                    // later launches are no-ops
+        if (PERSIST) {
+          // the pairs are not in step: [1] is the LATEST iteration in which one froze, whoever is counted last
+          ready_next = INT_MAX;
+          atomicMax(&a.w.counters[3], it + 1);
+          __threadfence();
+          const int nf = atomicAdd(&a.w.counters[0], 1) + 1;
+          if (nf == a.N) { __threadfence(); a.w.counters[1] = atomicMax(&a.w.counters[3], 0); }
+        } else {
+          const int nf = atomicAdd(&a.w.counters[0], 1) + 1;
+          if (nf == a.N) a.w.counters[1] = it + 1;                                  // later launches are no-ops
+        }
       }
     }
-    a.w.counters[2] = it + 1;
+    if (PERSIST) atomicMax(&a.w.counters[2], it + 1); else a.w.counters[2] = it + 1;
     allzero = (tot[NA + D + 1] == 0.0 && it > 0) ? 1 : 0;
   }
   allzero = __shfl_sync(0xffffffffu, allzero, 0);
   if (allzero) {                        // all weights zero: repeat the previous row (ICP.py:215-218)
     for (int r = lane; r < R; r += 32) wh[r] = wh[r - (ptrdiff_t)R];
   }
+  if (!PERSIST) return;
+  // the pair's next iteration may start: everything this block and (through the tickets) the pair's other
+  // blocks wrote is ordered before the flag
+  __threadfence();
+  __syncwarp();
+  if (lane == 0) st_release_gpu(a.w.ready + b, ready_next);
+  }
+#undef ROWS_NEXT
 }
 
 // ---------------------------------------------------------------------------------------------
 // finish: aligned cloud, T, stats
 // ---------------------------------------------------------------------------------------------
+// The persistent launch skips the items of a converged pair; the histories such a pair repeats from the iteration
+// after it froze to the last executed one (ICP.py:215-224, 246-247) are written here instead.
+struct FrozenFill { void* deltas; void* weights_hist; void* costs; int K, R, on; };
+
 template <typename T, int DIM>
 __global__ void icp_finish_kernel(const T* __restrict__ source, IcpWorkspace w, IcpSaved sv, int save, int N, int n,
                                   T* __restrict__ T_out, T* __restrict__ pc_out, uint8_t* converged, T* iterations,
-                                  T* matched_ratio, int32_t* iters_done) {
+                                  T* matched_ratio, int32_t* iters_done, FrozenFill ff) {
   const int b = blockIdx.x, tid = threadIdx.x;
   __shared__ double sP[12];
   if (tid < 12) sP[tid] = w.pose[(size_t)b * 12 + tid];
+  if (ff.on && w.frozen[b]) {
+    const int first = (int)w.num_iters[b], done = w.counters[2];      // froze in iteration first - 1
+    if (first >= 1 && first < done) {
+      T* wh = static_cast<T*>(ff.weights_hist) + (size_t)b * ff.K * ff.R;
+      const T* last = wh + (size_t)(first - 1) * ff.R;
+      for (int it = first; it < done; ++it)
+        for (int r = tid; r < ff.R; r += blockDim.x) wh[(size_t)it * ff.R + r] = last[r];
+      const int span = done - first;
+      T* dl = static_cast<T*>(ff.deltas) + ((size_t)b * ff.K + first) * 6;
+      for (int k = tid; k < span * 6; k += blockDim.x) dl[k] = (T)0;
+      T* cs = static_cast<T*>(ff.costs) + (size_t)b * ff.K;
+      const T pc0 = from_double<T>(w.prev_cost[b]);
+      for (int k = tid; k < span; k += blockDim.x) {
+        cs[first + k] = pc0;
+        if (save) sv.active[(size_t)(first + k) * N + b] = 0;
+      }
+    }
+  }
   __syncthreads();
+  if (ff.on && tid == 0 && w.frozen[b] && (int)w.num_iters[b] < w.counters[2]) w.n_matched[b] = 0;
   const T* src = source + (size_t)b * n * 3;
   T* pc = pc_out + (size_t)b * n * 3;
   for (int i = tid; i < n; i += blockDim.x) {
@@ -2285,9 +2381,32 @@ static int launch_grid_nn(const NNArgs& a, const IcpPlan& pl, const IcpWorkspace
   return check_launch();
 }
 
-template <typename T, int ICP, int DIM, bool FUSED>
+// blocks of the persistent launch: what the device holds at once (more would only queue behind them)
+template <typename T, int ICP, int DIM>
+static int rows_resident_blocks() {
+  static std::atomic<int> cached[64];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  int v = cached[dev].load(std::memory_order_relaxed);
+  if (!v) {
+    int sms = 0, per_sm = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, icp_rows_kernel<T, ICP, DIM, true, true>, GRID_ROWS_WARPS * 32, 0);
+    v = (sms > 0 ? sms : 148) * (per_sm > 0 ? per_sm : MMB_ROWS_MINBLOCKS);
+    cached[dev].store(v, std::memory_order_relaxed);
+  }
+  return v;
+}
+
+template <typename T, int ICP, int DIM, bool FUSED, bool PERSIST = false>
 static int launch_rows(const RowsArgs& ra, const IcpPlan& pl, int pdl, cudaStream_t st) {
   cudaLaunchConfig_t cfg = {};
+  if (PERSIST) {
+    const long long items = (long long)pl.nblk * pl.N * ra.K;
+    const int resident = rows_resident_blocks<T, ICP, DIM>();
+    cfg.gridDim = dim3((unsigned)(items < resident ? items : resident));
+  } else
   cfg.gridDim = MMB_ROWS_INTERLEAVE ? dim3((unsigned)pl.nblk * (unsigned)pl.N) : dim3((unsigned)pl.nblk, (unsigned)pl.N);
   cfg.blockDim = dim3(GRID_ROWS_WARPS * 32);
   cfg.dynamicSmemBytes = 0; cfg.stream = st;
@@ -2295,7 +2414,7 @@ static int launch_rows(const RowsArgs& ra, const IcpPlan& pl, int pdl, cudaStrea
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  cudaLaunchKernelEx(&cfg, icp_rows_kernel<T, ICP, DIM, FUSED>, ra);
+  cudaLaunchKernelEx(&cfg, icp_rows_kernel<T, ICP, DIM, FUSED, PERSIST>, ra);
   return check_launch();
 }
 
@@ -2392,12 +2511,20 @@ static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* s
     ra.N = pl.N; ra.n = pl.n; ra.m = pl.m; ra.cols = p->target_cols; ra.K = p->max_iterations;
     ra.const_iter = p->const_iter; ra.save = save; ra.has_weight = sa.has_weight; ra.nblk = pl.nblk;
     ra.tol = p->tolerance; ra.match_thresh = p->match_ratio_thresh;
+#if MMB_ROWS_PERSIST
+    // ... and one launch for all iterations: the blocks take (iteration, pair, query group) items off a queue
+    ra.it = 0; ra.warm = 0;
+    if (prof) prof->mark(2);
+    if ((rc = launch_rows<T, ICP, DIM, true, true>(ra, pl, 0, st))) return rc;
+    if (prof) prof->mark(0);
+#else
     for (int it = 0; it < p->max_iterations; ++it) {
       ra.it = it; ra.warm = it > 0 ? 1 : 0;
       if (prof && it == 0) prof->mark(2);
       if ((rc = launch_rows<T, ICP, DIM, true>(ra, pl, it > 0 ? 1 : 0, st))) return rc;
       if (prof) prof->mark(0);
     }
+#endif
   } else
   for (int it = 0; it < p->max_iterations; ++it) {
     na.idx_prev = it > 0 ? w.idx_cur : nullptr;
@@ -2422,10 +2549,13 @@ static int run_forward(const mmb_icp_params* p, const IcpPlan& pl, const void* s
     if ((rc = check_launch())) return rc;
     if (prof) prof->mark(1);
   }
+  FrozenFill ff;
+  ff.deltas = deltas; ff.weights_hist = weights_hist; ff.costs = costs; ff.K = p->max_iterations;
+  ff.R = pl.n * (ICP == MMB_PT2PT ? 3 : 1); ff.on = (pl.grid == 2 && MMB_ROWS_PERSIST) ? 1 : 0;
   icp_finish_kernel<T, DIM><<<pl.N, 256, 0, st>>>(static_cast<const T*>(source), w, sv, save, pl.N, pl.n,
                                                   static_cast<T*>(T_out), static_cast<T*>(pc_out), converged,
                                                   static_cast<T*>(iterations), static_cast<T*>(matched_ratio),
-                                                  iters_done);
+                                                  iters_done, ff);
   rc = check_launch();
   if (prof) prof->mark(2);
   return rc;
