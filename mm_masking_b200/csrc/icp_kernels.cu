@@ -176,6 +176,8 @@ struct IcpWorkspace {
   double* partials;              // (N, nblk, 32) per-block partial sums of the normal equations
   int* arrive;                   // (N) blocks of the pair that have parked their partials in this iteration
   int* ready;                    // (N) persistent launch: iterations of the pair that are complete (INT_MAX once it froze)
+  void* prevnn;                  // (N,n) the matched target of every query in the latest iteration: x, y, z, index (the layout
+                                 // of `sorted`) -- the warm start of the next search reads it without the index -> row gather
   size_t bytes;
 };
 
@@ -210,7 +212,9 @@ static IcpWorkspace carve_workspace(void* base, const IcpPlan& pl) {
   w.partials = c.take<double>(pl.grid == 2 ? (size_t)pl.N * pl.nblk * 32 : 0);
   w.arrive = c.take<int>(pl.grid == 2 ? pl.N : 0);
   w.ready = c.take<int>(pl.grid == 2 ? pl.N : 0);
-  if (pl.grid != 2) { w.arrive = nullptr; w.ready = nullptr; }   // take(0) is the END of the workspace, not "absent"
+  w.prevnn = pl.f64 ? static_cast<void*>(c.take<double>(pl.grid == 2 ? Nn * 4 : 0))
+                    : static_cast<void*>(c.take<float>(pl.grid == 2 ? Nn * 4 : 0));
+  if (pl.grid != 2) { w.arrive = nullptr; w.ready = nullptr; w.prevnn = nullptr; }   // take(0) is the END of the workspace, not "absent"
   w.bytes = c.off;
   return w;
 }
@@ -786,6 +790,24 @@ __device__ __forceinline__ void load_sorted(const SortedPoint<double>* p, double
   x = a.x; y = a.y; z = c.x; j = (int)__double_as_longlong(c.y);
 }
 
+// the previous match of a query (x, y, z, index): written by the row pass of one iteration, read by phase A of the
+// next on another SM -- through L2 (.cg), never a stale L1 line
+__device__ __forceinline__ void load_prev(const SortedPoint<float>* p, float& x, float& y, float& z, int& j) {
+  const float4 v = __ldcg(reinterpret_cast<const float4*>(p));
+  x = v.x; y = v.y; z = v.z; j = __float_as_int(v.w);
+}
+__device__ __forceinline__ void load_prev(const SortedPoint<double>* p, double& x, double& y, double& z, int& j) {
+  const double2 a = __ldcg(reinterpret_cast<const double2*>(p)), c = __ldcg(reinterpret_cast<const double2*>(p) + 1);
+  x = a.x; y = a.y; z = c.x; j = (int)__double_as_longlong(c.y);
+}
+__device__ __forceinline__ void store_prev(SortedPoint<float>* p, float x, float y, float z, int j) {
+  __stcg(reinterpret_cast<float4*>(p), make_float4(x, y, z, __int_as_float(j)));
+}
+__device__ __forceinline__ void store_prev(SortedPoint<double>* p, double x, double y, double z, int j) {
+  __stcg(reinterpret_cast<double2*>(p), make_double2(x, y));
+  __stcg(reinterpret_cast<double2*>(p) + 1, make_double2(z, __longlong_as_double((long long)j)));
+}
+
 struct GridNNArgs {
   const void* source; const void* target; const double* pose;
   const double* geom; const int* cell_start; const void* sorted;
@@ -1329,6 +1351,20 @@ __device__ __forceinline__ float sqrt_upper_ff(float v) {
   return r * 1.00000048f;
 }
 
+#ifndef MMB_ROWS_TRACE
+#define MMB_ROWS_TRACE 0                         // 1 (profiling builds only): per-item and per-query timestamps, profiles/rows_trace.py
+#endif
+#if MMB_ROWS_TRACE
+constexpr int ROWS_TRACE_ITEMS = 1 << 17;
+__device__ unsigned long long g_rows_trace[ROWS_TRACE_ITEMS][4];   // per item: asked the queue, got the number, pair ready, search ended
+__device__ unsigned int g_rows_qtrace[ROWS_TRACE_ITEMS * 32][4];   // per query: start, end (ns since the item was ready), walk rounds, warp
+__device__ __forceinline__ unsigned long long trace_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#endif
+
 __device__ __forceinline__ int ld_acquire_gpu(const int* p) {
   int v;
   asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -1364,15 +1400,27 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     // warp 1 takes the block's next item (and waits for the pair) while warp 0 may still be in the row pass of
     // the previous one; the barrier below is also what frees the previous item's shared state
     if (tid == 32) {
-      const int per = a.N * a.nblk;
-      int item = atomicAdd(&a.w.counters[4], 1);
-      if (item < a.K * per) {
+      const int per = a.N * a.nblk, total = a.K * per;
+      int item;
+      for (;;) {
+#if MMB_ROWS_TRACE
+        const unsigned long long t0 = trace_now();
+#endif
+        item = atomicAdd(&a.w.counters[4], 1);
+        if (item >= total) { item = -1; break; }
         const int it_ = item / per, b_ = (item - it_ * per) / a.nblk;
         const int stop = *reinterpret_cast<volatile int*>(a.w.counters + 1);
-        if (stop && it_ >= stop) item = -1;                  // every pair converged in an earlier iteration
-        else while (ld_acquire_gpu(a.w.ready + b_) < it_) __nanosleep(32);
-      } else {
-        item = -1;
+#if MMB_ROWS_TRACE
+        const unsigned long long t1 = trace_now();
+#endif
+        if (stop && it_ >= stop) { item = -1; break; }        // every pair converged in an earlier iteration
+        int r = ld_acquire_gpu(a.w.ready + b_);
+        while (r < it_) { __nanosleep(32); r = ld_acquire_gpu(a.w.ready + b_); }
+        if (r == INT_MAX) continue;                          // this pair converged (icp_finish_kernel repeats its histories)
+#if MMB_ROWS_TRACE
+        if (item < ROWS_TRACE_ITEMS) { g_rows_trace[item][0] = t0; g_rows_trace[item][1] = t1; g_rows_trace[item][2] = trace_now(); }
+#endif
+        break;
       }
       sItem = item;
     }
@@ -1381,10 +1429,6 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     if (item < 0) return;
     const int per = a.N * a.nblk;
     it = item / per; b = (item - it * per) / a.nblk; blk = item - it * per - b * a.nblk;
-    if (*reinterpret_cast<volatile int*>(a.w.frozen + b)) {   // converged: icp_finish_kernel repeats its histories
-      __syncthreads();                                        // sItem has been read by every warp
-      continue;
-    }
   } else {
     // consecutive blocks cycle through the pairs, so that at any moment (and in the tail of the launch) the
     // resident blocks are a mix of cheap (converged) and expensive (far from the map) pairs
@@ -1425,8 +1469,22 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
   __shared__ T sRow[GRID_ROWS_QB][6];               // matched target row of every query (fetched by the searching warp)
   struct Bases { const T* src; const T* tgt; const int* start; const void* sorted; };
   __shared__ Bases sB;
-  if (tid < 12) sP[tid] = a.w.pose[(size_t)b * 12 + tid];
-  if (tid < 4) sG[tid] = a.w.geom[(size_t)b * 4 + tid];
+  // The source point of the thread's query and the query's previous match are asked for BEFORE the pose and the
+  // barrier that publishes it: the three loads share one round trip to L2 (they used to be three dependent ones:
+  // pose -> barrier -> source point and previous index -> matched row).
+  T qs0 = (T)0, qs1 = (T)0, qs2 = (T)0, pvx = (T)0, pvy = (T)0, pvz = (T)0;
+  int pvj = -1;
+  if (FUSED) {
+    const int slot_ = warp * 4 + (lane >> 3), qi_ = q_first + slot_;
+    if (slot_ < GRID_ROWS_QB && qi_ < a.n) {
+      const size_t o_ = (size_t)b * a.n + qi_;
+      const T* sp = static_cast<const T*>(a.source) + o_ * 3;
+      qs0 = __ldg(sp); qs1 = __ldg(sp + 1); qs2 = __ldg(sp + 2);
+      if (warm) load_prev(static_cast<const SortedPoint<T>*>(a.w.prevnn) + o_, pvx, pvy, pvz, pvj);
+    }
+  }
+  if (tid < 12) sP[tid] = __ldcg(a.w.pose + (size_t)b * 12 + tid);
+  if (tid < 4) sG[tid] = __ldg(a.w.geom + (size_t)b * 4 + tid);
   if (tid == 32) {
     sB.src = static_cast<const T*>(a.source) + (size_t)b * a.n * 3;
     sB.tgt = static_cast<const T*>(a.target) + (size_t)b * a.m * a.cols;
@@ -1467,14 +1525,17 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     const int slot = warp * 4 + g, qi = q_first + slot;
     if (slot < GRID_ROWS_QB && qi < a.n) {                   // with more than QB / 4 warps the extra ones only search
       double qx, qy, qz;
-      transform_query<T, DIM>(src + (size_t)qi * 3, sP, qx, qy, qz);
       double D2 = 1.0e308; int I = INT_MAX;
-      if (warm) {
-        const int j0 = a.w.idx_cur[(size_t)b * a.n + qi];
-        if (j0 >= 0 && j0 < a.m) {
-          const double d0 = exact_dist2<T, DIM>(tgt + (size_t)j0 * a.cols, qx, qy, qz);
-          if (d0 < 1.0e300) { D2 = d0; I = j0; }
+      if (FUSED) {
+        const T q_src[3] = {qs0, qs1, qs2};
+        transform_query<T, DIM>(q_src, sP, qx, qy, qz);
+        if (warm && pvj >= 0 && pvj < a.m) {
+          const T row0[3] = {pvx, pvy, pvz};
+          const double d0 = exact_dist2<T, DIM>(row0, qx, qy, qz);
+          if (d0 < 1.0e300) { D2 = d0; I = pvj; }
         }
+      } else {
+        transform_query<T, DIM>(src + (size_t)qi * 3, sP, qx, qy, qz);
       }
       int2 runs[4] = {make_int2(0, 0), make_int2(0, 0), make_int2(0, 0), make_int2(0, 0)};
       int ylo = 0, yhi = -1;
@@ -1516,6 +1577,10 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     }
     if (slot >= nqb) break;
     const int qi = q_first + slot;
+#if MMB_ROWS_TRACE
+    const unsigned long long tq0 = trace_now();
+    unsigned int rounds = 0;
+#endif
     const double qx = sQ[0][slot], qy = sQ[1][slot], qz = sQ[2][slot];
     double D2 = sQ[3][slot]; int I = sI[slot];               // per-lane partial minimum (all lanes start equal)
     double fx = (qx - sG[0]) * sG[2], fy = (qy - sG[1]) * sG[2];
@@ -1595,6 +1660,9 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
           sa[k] = cs; cs = min(cs + 32, ce); ea[k] = cs;
         }
         if (sa[0] >= ea[0]) break;                           // nothing left
+#if MMB_ROWS_TRACE
+        ++rounds;
+#endif
         float4 v[MMB_ROWS_CH];
 #pragma unroll
         for (int k = 0; k < MMB_ROWS_CH; ++k) {
@@ -1717,6 +1785,16 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
         reduce();
       }
     }
+#if MMB_ROWS_TRACE
+    if (PERSIST && lane == 0) {
+      const int item_ = (it * a.N + b) * a.nblk + blk;
+      if (item_ < ROWS_TRACE_ITEMS) {
+        unsigned int* q = g_rows_qtrace[item_ * 32 + slot];
+        const unsigned long long base = g_rows_trace[item_][2];
+        q[0] = (unsigned int)(tq0 - base); q[1] = (unsigned int)(trace_now() - base); q[2] = rounds; q[3] = (unsigned int)warp;
+      }
+    }
+#endif
     if (FUSED) {
       // the matched row goes to shared memory now, under the search of the warp's next query, so that the row
       // pass below starts without a dependent gather
@@ -1728,6 +1806,12 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
   }
   if (!FUSED) return;
   __syncthreads();
+#if MMB_ROWS_TRACE
+  if (PERSIST && tid == 0) {
+    const int item_ = (it * a.N + b) * a.nblk + blk;
+    if (item_ < ROWS_TRACE_ITEMS) g_rows_trace[item_][3] = trace_now();
+  }
+#endif
   if (warp != 0) ROWS_NEXT
 
   // ------------------------- residual rows of the block's queries: one per lane -----------------
@@ -1741,7 +1825,6 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     const size_t o = (size_t)b * a.n + i;
     int j = sIdx[lane];
     if (j == INT_MAX) j = 0;
-    a.w.idx_cur[o] = j;
     if (a.save) a.sv.idx_hist[(size_t)it * a.N * a.n + o] = j;
     const double px = (double)src[i * 3 + 0], py = (double)src[i * 3 + 1];
     const double pz = DIM == 3 ? (double)src[i * 3 + 2] : 0.0;
@@ -1749,6 +1832,7 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     rotate_point(sP, px, py, pz, ax, ay, az);
     const double yx = __dadd_rn(ax, sP[9]), yy = __dadd_rn(ay, sP[10]), yz = __dadd_rn(az, sP[11]);
     const T* row = sRow[lane];
+    store_prev(static_cast<SortedPoint<T>*>(a.w.prevnn) + o, row[0], row[1], row[2], j);   // warm start of the next iteration
     const double dx = yx - (double)row[0], dy = yy - (double)row[1];
     const double dz = yz - (DIM == 3 ? (double)row[2] : 0.0);
     const double w0 = a.has_weight ? (double)static_cast<const T*>(a.weight)[o] : 1.0;
@@ -2838,6 +2922,16 @@ int mmb_nn_search_static(int32_t N, int32_t n, int32_t m, int32_t target_cols, i
   return dim == 2 ? run_nn_search<double, 2>(pl, target_cols, dim, query, target, idx_out, w, st)
                   : run_nn_search<double, 3>(pl, target_cols, dim, query, target, idx_out, w, st);
 }
+
+#if MMB_ROWS_TRACE
+// profiling builds only (not declared in the header, not in the shipped library)
+int mmb_debug_rows_trace(void* host_out, size_t bytes) {
+  return cudaMemcpyFromSymbol(host_out, g_rows_trace, bytes) == cudaSuccess ? MMB_OK : MMB_ERR_CUDA;
+}
+int mmb_debug_rows_qtrace(void* host_out, size_t bytes) {
+  return cudaMemcpyFromSymbol(host_out, g_rows_qtrace, bytes) == cudaSuccess ? MMB_OK : MMB_ERR_CUDA;
+}
+#endif
 
 int mmb_fp32_probe(int32_t blocks, int32_t iters, int32_t packed, float* out, void* stream) {
   if (!out || blocks <= 0 || iters <= 0) return MMB_ERR_INVALID_SHAPE;
