@@ -61,14 +61,25 @@ NN_BACKENDS = {"auto": 0, "brute": 1, "grid": 2, "rows": 3}
 FLOP_PER_PAIR = 8          # 3 sub, 3 mul, 2 add: the distance `torch.cdist` evaluates
 
 
-def kernel_source_sha():
-    """sha256 (first 16 hex) over the CUDA sources: the key that ties an ncu capture in profiles/traffic.json to
-    the binary that is being timed"""
+def kernel_source_file(kernel):
+    """the .cu file under mm_masking_b200/csrc that defines `kernel` (None if none does)"""
+    d = os.path.join(ROOT, "mm_masking_b200", "csrc")
+    for f in sorted(os.listdir(d)):
+        if f.endswith(".cu") and (" " + kernel + "(") in open(os.path.join(d, f)).read():
+            return f
+    return None
+
+
+def kernel_source_sha(kernel=None):
+    """sha256 (first 16 hex) over the CUDA sources a kernel is built from -- the shared headers and the .cu file that
+    defines it (every .cu when `kernel` is None or unknown): the key that ties an ncu capture in
+    profiles/traffic.json to the binary that is being timed"""
     import hashlib
     h = hashlib.sha256()
     d = os.path.join(ROOT, "mm_masking_b200", "csrc")
+    own = kernel_source_file(kernel) if kernel else None
     for f in sorted(os.listdir(d)):
-        if f.endswith((".cu", ".cuh")):
+        if f.endswith(".cuh") or (f.endswith(".cu") and (own is None or f == own)):
             h.update(open(os.path.join(d, f), "rb").read())
     return h.hexdigest()[:16]
 
@@ -77,7 +88,7 @@ def traffic_lookup(kernel, workload):
     """DRAM bytes per launch of `kernel` at `workload` from the committed ncu captures (profiles/traffic.json,
     written by profiles/ncu_summarise.py).  Returns (bytes or None, info dict)."""
     path = os.path.join(ROOT, "profiles", "traffic.json")
-    sha = kernel_source_sha()
+    sha = kernel_source_sha(kernel)
     if not os.path.exists(path):
         return None, {"traffic_stale": True, "traffic_source": "profiles/traffic.json missing"}
     best = None

@@ -83,6 +83,10 @@ static_assert(GRID_STRIDE >= GRID_CELLS + GRID_TAIL + 1 && GRID_STRIDE % 4 == 0,
 #ifndef MMB_ROWS_PERSIST
 #define MMB_ROWS_PERSIST 1                       // 1: one launch runs all iterations (work queue + per-pair ready flags)
 #endif
+#ifndef MMB_ROWS_EARLY_FETCH
+#define MMB_ROWS_EARLY_FETCH 0                   // 1: the next item is taken off the queue at the end of the search (measured
+                                                 // slower, 0.560 vs 0.544 ms at c3: an item held even 2 us delays its pair)
+#endif
 #ifndef MMB_ROWS_INTERLEAVE
 #define MMB_ROWS_INTERLEAVE 0
 #endif
@@ -1393,30 +1397,44 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int R = a.n * ROWS;
   __shared__ int sItem;
+  // one item off the queue and the progress of its pair (thread 32 only): -1 = nothing left
+  auto fetch_item = [&](int& item, int& r) {
+    const int per = a.N * a.nblk;
+    const int stop = *reinterpret_cast<volatile int*>(a.w.counters + 1);     // in flight together with the atomic
+    item = atomicAdd(&a.w.counters[4], 1);
+    r = 0;
+    if (item >= a.K * per) { item = -1; return; }
+    const int it_ = item / per;
+    if (stop && it_ >= stop) { item = -1; return; }          // every pair converged in an earlier iteration
+    r = ld_acquire_gpu(a.w.ready + (item - it_ * per) / a.nblk);
+  };
+  int nx_item = -3, nx_ready = 0;                             // thread 32: the item fetched ahead (-3: none)
 #define ROWS_NEXT { if (PERSIST) continue; else return; }
   for (;;) {
   int it, b, blk;
   if (PERSIST) {
     // warp 1 takes the block's next item (and waits for the pair) while warp 0 may still be in the row pass of
     // the previous one; the barrier below is also what frees the previous item's shared state
+    // Thread 32 takes the block's next item off the queue while warp 0 is still in the row pass of the previous
+    // one, and waits until the pair's previous iteration is complete.  (With MMB_ROWS_EARLY_FETCH the number was
+    // asked for at the end of the search below; the wait is never done there, where it would hold up the row pass
+    // of an item that very iteration may be waiting for.)
     if (tid == 32) {
-      const int per = a.N * a.nblk, total = a.K * per;
-      int item;
+      const int per = a.N * a.nblk;
+      int item = nx_item, r = nx_ready;
+      nx_item = -3;
       for (;;) {
 #if MMB_ROWS_TRACE
         const unsigned long long t0 = trace_now();
 #endif
-        item = atomicAdd(&a.w.counters[4], 1);
-        if (item >= total) { item = -1; break; }
+        if (item == -3) fetch_item(item, r);
+        if (item < 0) break;                                 // the queue is empty / every pair has converged
         const int it_ = item / per, b_ = (item - it_ * per) / a.nblk;
-        const int stop = *reinterpret_cast<volatile int*>(a.w.counters + 1);
 #if MMB_ROWS_TRACE
         const unsigned long long t1 = trace_now();
 #endif
-        if (stop && it_ >= stop) { item = -1; break; }        // every pair converged in an earlier iteration
-        int r = ld_acquire_gpu(a.w.ready + b_);
         while (r < it_) { __nanosleep(32); r = ld_acquire_gpu(a.w.ready + b_); }
-        if (r == INT_MAX) continue;                          // this pair converged (icp_finish_kernel repeats its histories)
+        if (r == INT_MAX) { item = -3; continue; }           // this pair converged (icp_finish_kernel repeats its histories)
 #if MMB_ROWS_TRACE
         if (item < ROWS_TRACE_ITEMS) { g_rows_trace[item][0] = t0; g_rows_trace[item][1] = t1; g_rows_trace[item][2] = trace_now(); }
 #endif
@@ -1805,6 +1823,7 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     }
   }
   if (!FUSED) return;
+  if (PERSIST && MMB_ROWS_EARLY_FETCH && tid == 32) fetch_item(nx_item, nx_ready);
   __syncthreads();
 #if MMB_ROWS_TRACE
   if (PERSIST && tid == 0) {
@@ -1947,7 +1966,7 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     for (int k = 0; k < 3; ++k) P[9 + k] = sP[9 + k] - d6[3 + k];
     for (int k = 0; k < 6; ++k) dl[k] = from_double<T>(d6[k]);
     double cost = tot[NA + D + 0];
-    if (cost == 0.0 && it > 0) cost = a.w.prev_cost[b];                             // ICP.py:220-222
+    if (cost == 0.0 && it > 0) cost = __ldcg(a.w.prev_cost + b);                    // ICP.py:220-222
     a.w.prev_cost[b] = cost;
     *cs = from_double<T>(cost);
     const int matched = (int)(tot[NA + D + 2] + 0.5), at_start = (int)(tot[NA + D + 3] + 0.5);
@@ -1960,8 +1979,8 @@ __global__ void __launch_bounds__(GRID_ROWS_WARPS * 32, MMB_ROWS_MINBLOCKS) icp_
     if (small) {
       a.w.conv[b] = 1;
       if (!a.const_iter) {                                                          // ICP.py:230-247
-        if (a.w.num_iters[b] == 0.0) a.w.num_iters[b] = (double)(it + 1);
-        if (a.w.match_ratio[b] == 0.0) a.w.match_ratio[b] = (double)matched / (double)(at_start > 0 ? at_start : 1);
+        if (__ldcg(a.w.num_iters + b) == 0.0) a.w.num_iters[b] = (double)(it + 1);
+        if (__ldcg(a.w.match_ratio + b) == 0.0) a.w.match_ratio[b] = (double)matched / (double)(at_start > 0 ? at_start : 1);
         a.w.frozen[b] = 1;
         if (PERSIST) {
           // the pairs are not in step: [1] is the LATEST iteration in which one froze, whoever is counted last

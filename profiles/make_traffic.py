@@ -32,7 +32,7 @@ def to_bytes(val, unit):
 
 def main():
     import bench
-    sha = bench.kernel_source_sha()
+    shas = {}
     entries = {}
     for arg in sys.argv[1:]:
         workload, report = arg.split("=", 1)
@@ -42,7 +42,10 @@ def main():
             rd = to_bytes(*r["dram__bytes_read.sum"]); wr = to_bytes(*r["dram__bytes_write.sum"])
             dur = float(r["gpu__time_duration.sum"][0].replace(",", ""))
             dur_us = dur if r["gpu__time_duration.sum"][1] == "us" else dur * {"ns": 1e-3, "ms": 1e3}[r["gpu__time_duration.sum"][1]]
-            e = entries.setdefault((base, workload), {"kernel": base, "instance": name, "workload": workload, "source_sha": sha,
+            if base not in shas:
+                shas[base] = bench.kernel_source_sha(base)
+            e = entries.setdefault((base, workload), {"kernel": base, "instance": name, "workload": workload, "source_sha": shas[base],
+                                                      "source_file": bench.kernel_source_file(base),
                                                       "capture": "profiles/" + os.path.basename(report).replace(".ncu-rep", "_summary.md"),
                                                       "launches": 0, "dram_read": 0.0, "dram_write": 0.0, "duration_us": 0.0,
                                                       "inst": 0.0})
