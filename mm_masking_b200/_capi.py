@@ -127,10 +127,17 @@ def check(status: int, what: str):
     raise MmbError(f"{what} failed: {msg}")
 
 
+_cuda_ok = False
+
+
 def require_cuda():
+    global _cuda_ok
+    if _cuda_ok:
+        return
     import torch
     if not torch.cuda.is_available():
         raise MmbError("mm_masking_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    _cuda_ok = True
 
 
 def ptr(t):
@@ -138,5 +145,23 @@ def ptr(t):
 
 
 def stream_ptr():
+    """the current CUDA stream of the current device as a raw `cudaStream_t` (no Stream object is built)"""
     import torch
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return C.c_void_p(torch._C._cuda_getCurrentRawStream(torch.cuda.current_device()))
+
+
+class _Here:
+    """no-op context: the tensor's device is already the current one"""
+    def __enter__(self):
+        return self
+    def __exit__(self, *exc):
+        return False
+
+
+_HERE = _Here()
+
+
+def on_device(dev):
+    """`torch.cuda.device(dev)` only when `dev` is not the current device (the context manager costs ~10 us a call)"""
+    import torch
+    return _HERE if dev.index is None or dev.index == torch.cuda.current_device() else torch.cuda.device(dev)
