@@ -542,6 +542,41 @@ def run_ours(args, wl, rank, world, local_rank):
     launches0 = lib.mmb_launch_count()
     ms_res, t0, t1 = timed(step_resident, args.steps, args.warmup)
     launches_resident = lib.mmb_launch_count() - launches0          # includes the W warm-up steps
+
+    # The same resident step captured ONCE in a CUDA graph and replayed (const_iter: the call path has no host
+    # synchronisation; tests/test_graph_capture_gpu.py checks replay == eager bit for bit).  Reported beside `value`,
+    # which stays the eager call: it shows what is left when the host's share of issuing a step is taken out.
+    graphed, per_rank_eager = None, list(per_rank)
+    g = None
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+
+        def step_for_capture():
+            out = alg.icp(d_src, d_tgt, d_T0, weight=d_w, **call)
+            return out["T"], torch.autograd.grad(out["T"].sum(), d_w)[0]
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                step_for_capture()
+        torch.cuda.current_stream().wait_stream(side)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            g_T, g_gw = step_for_capture()
+    except Exception as exc:                                         # informational: never fails the bench
+        graphed, g = {"error": repr(exc)[:200]}, None
+    # every rank takes the timed loop (it holds barriers) or none does
+    if mdist.max_over_ranks(0.0 if g is not None else 1.0, device=dev) == 0.0:
+        ms_graph, _, _ = timed(g.replay, args.steps, args.warmup)
+        eager = step_resident()
+        torch.cuda.synchronize()
+        graphed = {"ms_per_step": ms_graph, "value": world * N / (ms_graph * 1e-3), "unit": UNIT,
+                   "same_as_eager": bool(torch.equal(g_T, eager["T"]) and torch.equal(g_gw, d_w.grad)),
+                   "per_rank_ms_per_step": list(per_rank),
+                   "how": "forward + backward of the resident step captured with torch.cuda.graph, one replay per step"}
+    elif graphed is None:
+        graphed = {"error": "capture failed on another rank"}
+    del g
+    per_rank.clear(); per_rank.extend(per_rank_eager)
     # e2e: the same call fed from pinned HOST tensors through the package's DevicePrefetcher (what
     # a user's loop does): every step uploads its own source/target/T_init/weight (no reuse across
     # steps; the upload of step k+1 runs on a copy stream under the kernels of step k) and reads T
@@ -753,6 +788,7 @@ def run_ours(args, wl, rank, world, local_rank):
         # library itself (mmb_launch_count differenced around the regions; warm-up steps excluded pro rata)
         "gpu_launches": int(launches_resident * args.steps // (args.steps + args.warmup) + launches_e2e),
         "gpu_launches_per_step": launches_resident // (args.steps + args.warmup),
+        "graphed": graphed,
         "roofline": roofline,
         "roofline_exhaustive_nn": roofline_brute,
         "cpu_baseline": cpu,
