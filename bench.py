@@ -10,20 +10,22 @@ per-point weight gradients the UNet needs are produced.  Workload c3 (BASELINE.j
 configs[2]): 32 pairs per GPU, 2 000 radar points vs 50 000 lidar map points, 10 iterations
 (`const_iter: True` so every pair does all 10).
 
-  value  pairs/s with inputs resident in HBM (CUDA events per step, L2 flushed between steps)
+  value  pairs/s with inputs resident in HBM (CUDA events per step, L2 flushed between steps): the step captured
+         once with torch.cuda.graph and replayed (every kernel runs on every replay; checked equal to the eager call;
+         falls back to the eager loop if the capture fails, --no-graph forces it); `eager` = the eager loop
   e2e    pairs/s through the same public call with HOST (pinned) inputs: H2D of source, target,
          T_init, weight and D2H of T and d(loss)/d(weight) inside the timed region, every step;
          fed through mm_masking_b200.prefetch.DevicePrefetcher (the upload of step k+1 runs on a
          copy stream under the kernels of step k); one event pair around all K steps
-  roofline       the dominant kernel of the default path, the exact cell-grid search
-                 (nn_grid_kernel): algorithmic bytes per launch / its CUDA-event duration against
-                 the measured HBM peak, flagged work-avoiding
+  roofline       the dominant kernel of the default path, the exact row-major cell-grid search fused with the ICP
+                 step (icp_rows_kernel, one persistent launch for all iterations): algorithmic bytes per launch /
+                 its CUDA-event duration against the measured HBM peak, flagged work-avoiding
   roofline_exhaustive_nn   the exhaustive kernel (nn_search_kernel, --nn-backend brute) on the
                  same data in the same run: 8 flop per (source, target) pair per launch / its
                  CUDA-event duration, against the FP32 FMA-pipe rate measured in the same run by
                  mmb_fp32_probe (MEASURED_PEAKS.json has no CUDA-core FP32 figure)
-  cpu_baseline   the oracle port of the reference algorithm (torch CPU, `torch.cdist` +
-                 `argmin` exactly as `external/dICP/dICP/nn.py:32-38`) on the box's host cores
+  cpu_baseline   the unmodified reference (oracle/_ref/dicp_ref, torch CPU) on the box's host cores, or the
+                 oracle port when that copy is absent (`kind` says which)
 
 Multi-GPU (torchrun): pairs are independent, so each rank runs its own 32 pairs and there is no
 data-path collective; value = all ranks' pairs / max-over-ranks time ("weak").
