@@ -562,7 +562,9 @@ def run_ours(args, wl, rank, world, local_rank):
                 step_for_capture()
         torch.cuda.current_stream().wait_stream(side)
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
+        # thread_local: a CUDA call from another thread of the process (the NCCL watchdog polling its events, the
+        # pinned-memory allocator) must not invalidate the capture
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
             g_T, g_gw = step_for_capture()
     except Exception as exc:                                         # informational: never fails the bench
         graphed, g = {"error": repr(exc)[:200]}, None
